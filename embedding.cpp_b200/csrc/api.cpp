@@ -1,0 +1,310 @@
+// api.cpp -- the bert.h exports of libbert.so (include/bert.h) on top of the CUDA engine (bk_api.h).
+//
+// Host-side replacement of the reference's model layer: bert_loader / bert_load_from_file
+// (bert.cpp:143-659, 783-819), bert_eval / bert_eval_batch (bert.cpp:1020-1108), bert_encode_batch
+// (bert.cpp:1119-1198), bert_tokenize (bert.cpp:738-781).  Where the reference loops over sentences and
+// builds one CPU graph each (bert.cpp:1065), this layer sorts the sentences by length, packs them
+// into token-budget micro-batches and deals those to one engine per GPU (sentences are independent:
+// no collective, host-side gather only).
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <numeric>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/bert.h"
+#include "../../include/bk_api.h"
+#include "gguf.h"
+#include "tokenizer_wp.h"
+
+using namespace bk;
+
+struct bert_ctx {
+    GgufFile file;
+    bk_hparams hp{};
+    std::vector<std::string> vocab;
+    int32_t cls_id = -1, sep_id = -1, pad_id = -1, unk_id = 0;  // defaults bert.cpp:119-124
+    WordPieceTokenizer tok;
+    bool tok_ok = false;
+    std::vector<bk_engine *> engines;
+    int cap_tokens = 0, cap_seqs = 0;
+    std::mutex mu;  // one in-flight call per context (the reference is not re-entrant either, bert.cpp:1056-1062)
+};
+
+namespace {
+
+int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// canonical tensor order of bert.cpp:623-652 == slot order of bk_engine_set_tensor
+std::vector<std::string> tensor_names(int n_layer) {
+    std::vector<std::string> n = {"embeddings.word_embeddings.weight", "embeddings.token_type_embeddings.weight",
+                                  "embeddings.position_embeddings.weight", "embeddings.LayerNorm.weight", "embeddings.LayerNorm.bias"};
+    static const char *per[16] = {"attention.self.query.weight", "attention.self.query.bias", "attention.self.key.weight",
+                                  "attention.self.key.bias", "attention.self.value.weight", "attention.self.value.bias",
+                                  "attention.output.dense.weight", "attention.output.dense.bias", "attention.output.LayerNorm.weight",
+                                  "attention.output.LayerNorm.bias", "intermediate.dense.weight", "intermediate.dense.bias",
+                                  "output.dense.weight", "output.dense.bias", "output.LayerNorm.weight", "output.LayerNorm.bias"};
+    for (int l = 0; l < n_layer; l++)
+        for (int k = 0; k < 16; k++) n.push_back("encoder.layer." + std::to_string(l) + "." + per[k]);
+    return n;
+}
+
+std::vector<int> pick_devices() {
+    std::vector<int> devs;
+    const int n = bk_device_count();
+    if (n <= 0) return devs;
+    if (const char *s = getenv("BERT_B200_DEVICES")) {
+        const char *p = s;
+        while (*p) {
+            char *end;
+            long v = strtol(p, &end, 10);
+            if (end == p) break;
+            if (v >= 0 && v < n) devs.push_back((int)v);
+            p = (*end == ',') ? end + 1 : end;
+        }
+        if (!devs.empty()) return devs;
+    }
+    int use = env_int("BERT_B200_NGPU", n);
+    if (use < 1) use = 1;
+    if (use > n) use = n;
+    for (int i = 0; i < use; i++) devs.push_back(i);
+    return devs;
+}
+
+struct MicroBatch { int begin, end, tokens; };  // range in the length-sorted order
+
+}  // namespace
+
+extern "C" {
+
+BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
+    std::unique_ptr<bert_ctx> ctx(new bert_ctx());
+    std::string err;
+    if (!ctx->file.open(fname, err)) { fprintf(stderr, "%s: failed to load '%s': %s\n", __func__, fname, err.c_str()); return nullptr; }
+    const GgufFile &g = ctx->file;
+    uint32_t v;
+    bk_hparams &hp = ctx->hp;
+    // llm_load_hparams, bert.cpp:496-513
+    const GgufValue *toks = g.find("tokenizer.ggml.tokens");
+    if (!toks || toks->type != GT_ARR || toks->elem_type != GT_STR) { fprintf(stderr, "%s: key not found in model: tokenizer.ggml.tokens\n", __func__); return nullptr; }
+    ctx->vocab = toks->strs;
+    hp.n_vocab = (int32_t)ctx->vocab.size();
+    struct { const char *key; int32_t *dst; } req[] = {{"bert.context_length", &hp.n_max_tokens}, {"bert.embedding_length", &hp.n_embd},
+                                                       {"bert.feed_forward_length", &hp.n_intermediate}, {"bert.attention.head_count", &hp.n_head},
+                                                       {"bert.block_count", &hp.n_layer}};
+    for (auto &r : req) {
+        if (!g.get_u32(r.key, v)) { fprintf(stderr, "%s: key not found in model: %s\n", __func__, r.key); return nullptr; }
+        *r.dst = (int32_t)v;
+    }
+    if (!g.get_f32("bert.attention.layer_norm_epsilon", hp.eps)) { fprintf(stderr, "%s: key not found in model: bert.attention.layer_norm_epsilon\n", __func__); return nullptr; }
+    if (hp.n_layer < 1 || hp.n_embd < 1 || hp.n_head < 1 || hp.n_max_tokens < 1) { fprintf(stderr, "%s: invalid hyper-parameters\n", __func__); return nullptr; }
+    // llm_load_tokenizer, bert.cpp:515-578 (special ids optional)
+    if (g.get_u32("tokenizer.ggml.cls_token_id", v)) ctx->cls_id = (int32_t)v;
+    if (g.get_u32("tokenizer.ggml.seperator_token_id", v)) ctx->sep_id = (int32_t)v;  // (sic) gguf.h:297
+    if (g.get_u32("tokenizer.ggml.padding_token_id", v)) ctx->pad_id = (int32_t)v;
+    if (g.get_u32("tokenizer.ggml.unknown_token_id", v)) ctx->unk_id = (int32_t)v;
+    if (const GgufValue *blob = g.find("blob.tokenizer.json")) {
+        std::string terr;
+        ctx->tok_ok = ctx->tok.load(blob->s, terr);
+        if (!ctx->tok_ok) fprintf(stderr, "%s: warning: tokenizer.json not usable (%s); bert_tokenize/bert_encode disabled\n", __func__, terr.c_str());
+    }
+    // file type = most frequent tensor type among 2-D tensors (bert.cpp:206-252 counts all tensors; the
+    // 2-D ones decide which GEMM path is used and are what the converter/quantiser change)
+    const std::vector<std::string> names = tensor_names(hp.n_layer);
+    int cnt[4] = {0, 0, 0, 0};
+    for (const auto &nm : names) {
+        const GgufTensor *t = g.tensor(nm);
+        if (!t) { fprintf(stderr, "%s: tensor '%s' not found\n", __func__, nm.c_str()); return nullptr; }
+        if (t->type > 3 || t->nbytes == 0) { fprintf(stderr, "%s: tensor '%s' has unsupported type %u (supported: F32, F16, Q4_0, Q4_1)\n", __func__, nm.c_str(), t->type); return nullptr; }
+        if (t->n_dims == 2) cnt[t->type]++;
+    }
+    hp.wtype = (int32_t)(std::max_element(cnt, cnt + 4) - cnt);
+
+    const std::vector<int> devs = pick_devices();
+    if (devs.empty()) { fprintf(stderr, "%s: no usable CUDA device (%s); this library has no CPU path\n", __func__, bk_last_error()); return nullptr; }
+    ctx->cap_tokens = env_int("BERT_B200_MB_TOKENS", 32768);
+    if (ctx->cap_tokens < hp.n_max_tokens) ctx->cap_tokens = hp.n_max_tokens;
+    ctx->cap_seqs = std::min(ctx->cap_tokens, env_int("BERT_B200_MB_SEQS", 8192));
+    for (int dev : devs) {
+        bk_engine *e = bk_engine_create(dev, &hp, ctx->cap_tokens, ctx->cap_seqs);
+        if (!e) { fprintf(stderr, "%s: engine on device %d: %s\n", __func__, dev, bk_last_error()); bert_free(ctx.release()); return nullptr; }
+        ctx->engines.push_back(e);
+        for (size_t i = 0; i < names.size(); i++) {
+            const GgufTensor *t = g.tensor(names[i]);
+            if (bk_engine_set_tensor(e, (int)i, (int)t->type, g.tensor_data(*t), (int64_t)t->ne[0], t->n_dims > 1 ? (int64_t)t->ne[1] : 1) != 0) {
+                fprintf(stderr, "%s: tensor '%s': %s\n", __func__, names[i].c_str(), bk_last_error());
+                bert_free(ctx.release());
+                return nullptr;
+            }
+        }
+        if (bk_engine_finalize(e) != 0) { fprintf(stderr, "%s: %s\n", __func__, bk_last_error()); bert_free(ctx.release()); return nullptr; }
+    }
+    if (env_int("BERT_B200_VERBOSE", 0))
+        fprintf(stderr, "%s: %s: d=%d f=%d heads=%d layers=%d vocab=%d wtype=%d on %zu GPU(s), micro-batch %d tokens\n", __func__, fname,
+                hp.n_embd, hp.n_intermediate, hp.n_head, hp.n_layer, hp.n_vocab, hp.wtype, ctx->engines.size(), ctx->cap_tokens);
+    return ctx.release();
+}
+
+BERT_API void bert_free(struct bert_ctx *ctx) {
+    if (!ctx) return;
+    for (bk_engine *e : ctx->engines) bk_engine_destroy(e);
+    delete ctx;
+}
+
+BERT_API int32_t bert_n_embd(struct bert_ctx *ctx) { return ctx->hp.n_embd; }
+BERT_API int32_t bert_n_max_tokens(struct bert_ctx *ctx) { return ctx->hp.n_max_tokens; }
+BERT_API const char *bert_vocab_id_to_token(struct bert_ctx *ctx, bert_vocab_id id) {
+    if (id < 0 || id >= (int32_t)ctx->vocab.size()) return nullptr;
+    return ctx->vocab[id].c_str();
+}
+
+BERT_API void bert_eval_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n_batch_size, bert_vocab_id **batch_tokens,
+                              int32_t *n_tokens, float **batch_embeddings) {
+    (void)n_threads;
+    if (!ctx || n_batch_size <= 0) return;
+    if (!batch_embeddings) return;  // memory-probe mode of the reference (bert.cpp:1039): nothing to measure here
+    const int N = ctx->hp.n_max_tokens, d = ctx->hp.n_embd;
+    for (int b = 0; b < n_batch_size; b++) {
+        if (n_tokens[b] > N) { fprintf(stderr, "Too many tokens, maximum is %d\n", N); return; }  // bert.cpp:1071-1075
+        if (n_tokens[b] < 1) { fprintf(stderr, "Empty input %d: at least one token is required\n", b); return; }
+    }
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    // length-sorted order (longest first), then token-budget micro-batches
+    std::vector<int> order(n_batch_size);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return n_tokens[a] > n_tokens[b]; });
+    long long total = 0;
+    for (int b = 0; b < n_batch_size; b++) total += n_tokens[b];
+    const int n_eng = (int)ctx->engines.size();
+    long long budget = ctx->cap_tokens;
+    if (n_eng > 1) budget = std::min<long long>(budget, std::max<long long>((total + n_eng - 1) / n_eng, N));
+    std::vector<MicroBatch> mbs;
+    for (int i = 0; i < n_batch_size;) {
+        int j = i, t = 0;
+        while (j < n_batch_size && j - i < ctx->cap_seqs && t + n_tokens[order[j]] <= budget) { t += n_tokens[order[j]]; j++; }
+        mbs.push_back({i, j, t});
+        i = j;
+    }
+    std::atomic<int> next{0};
+    std::atomic<int> failed{0};
+    auto worker = [&](int ei) {
+        bk_engine *e = ctx->engines[ei];
+        std::vector<int32_t> toks, lens;
+        std::vector<float> out;
+        for (;;) {
+            const int m = next.fetch_add(1);
+            if (m >= (int)mbs.size() || failed.load()) break;
+            const MicroBatch &mb = mbs[m];
+            const int ns = mb.end - mb.begin;
+            toks.resize(mb.tokens); lens.resize(ns); out.resize((size_t)ns * d);
+            int off = 0;
+            for (int s = 0; s < ns; s++) {
+                const int b = order[mb.begin + s];
+                lens[s] = n_tokens[b];
+                memcpy(toks.data() + off, batch_tokens[b], (size_t)n_tokens[b] * sizeof(int32_t));
+                off += n_tokens[b];
+            }
+            if (bk_engine_forward(e, toks.data(), lens.data(), ns, out.data()) != 0) {
+                fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error());
+                failed.store(1);
+                break;
+            }
+            for (int s = 0; s < ns; s++) memcpy(batch_embeddings[order[mb.begin + s]], out.data() + (size_t)s * d, (size_t)d * sizeof(float));
+        }
+    };
+    const int n_workers = std::min<int>(n_eng, (int)mbs.size());
+    if (n_workers <= 1) worker(0);
+    else {
+        std::vector<std::thread> th;
+        for (int i = 1; i < n_workers; i++) th.emplace_back(worker, i);
+        worker(0);
+        for (auto &t : th) t.join();
+    }
+}
+
+BERT_API void bert_eval(struct bert_ctx *ctx, int32_t n_threads, bert_vocab_id *tokens, int32_t n_tokens, float *embeddings) {
+    bert_eval_batch(ctx, n_threads, 1, &tokens, &n_tokens, embeddings ? &embeddings : nullptr);  // bert.cpp:1020-1028
+}
+
+BERT_API void bert_tokenize(struct bert_ctx *ctx, const char *text, bert_vocab_id *tokens, int32_t *n_tokens, int32_t n_max_tokens) {
+    // bert.cpp:738-781: [CLS] + ids (stop at the first PAD id or when full) + [SEP]; when full the last slot is SEP
+    *n_tokens = 0;
+    if (n_max_tokens < 2) return;
+    std::vector<int32_t> ids;
+    if (ctx->tok_ok) ids = ctx->tok.encode(text ? text : "");
+    int t = 0;
+    tokens[t++] = ctx->cls_id;
+    for (int32_t id : ids) {
+        if (id == ctx->pad_id) break;
+        if (t >= n_max_tokens) break;
+        tokens[t++] = id;
+    }
+    if (t >= n_max_tokens) tokens[n_max_tokens - 1] = ctx->sep_id;
+    else tokens[t++] = ctx->sep_id;
+    *n_tokens = t;
+}
+
+BERT_API void bert_encode_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n_batch_size, int32_t n_inputs, const char **texts,
+                                float **embeddings) {
+    (void)n_batch_size;  // the reference overrides it to 1 (bert.cpp:1128); here the whole call is one sorted batch
+    if (!ctx || n_inputs <= 0) return;
+    const int N = ctx->hp.n_max_tokens;
+    std::vector<int32_t> buf((size_t)n_inputs * N);
+    std::vector<int32_t *> ptrs(n_inputs);
+    std::vector<int32_t> lens(n_inputs);
+    // tokenisation is independent per text: spread it over host threads when the batch is large
+    const int hw = (int)std::max(1u, std::thread::hardware_concurrency());
+    const int nt = std::max(1, std::min({hw, n_inputs / 64, 32}));
+    auto tok_range = [&](int lo, int hi) {
+        for (int i = lo; i < hi; i++) {
+            ptrs[i] = buf.data() + (size_t)i * N;
+            bert_tokenize(ctx, texts[i], ptrs[i], &lens[i], N);
+        }
+    };
+    if (nt <= 1) tok_range(0, n_inputs);
+    else {
+        std::vector<std::thread> th;
+        const int per = (n_inputs + nt - 1) / nt;
+        for (int t = 0; t < nt; t++) th.emplace_back(tok_range, t * per, std::min(n_inputs, (t + 1) * per));
+        for (auto &t : th) t.join();
+    }
+    bert_eval_batch(ctx, n_threads, n_inputs, ptrs.data(), lens.data(), embeddings);
+}
+
+BERT_API void bert_encode(struct bert_ctx *ctx, int32_t n_threads, const char *texts, float *embeddings) {
+    bert_encode_batch(ctx, n_threads, 1, 1, &texts, &embeddings);  // bert.cpp:1110-1117
+}
+
+}  // extern "C"
+
+// bert.cpp:681-733
+static void bert_print_usage(char **argv, const bert_params &params) {
+    fprintf(stderr, "usage: %s [options]\n\noptions:\n", argv[0]);
+    fprintf(stderr, "  -h, --help            show this help message and exit\n");
+    fprintf(stderr, "  -t N, --threads N     number of threads to use during computation (default: %d)\n", params.n_threads);
+    fprintf(stderr, "  -p PROMPT, --prompt PROMPT\n                        prompt to start generation with (default: random)\n");
+    fprintf(stderr, "  --port p     port to bind in server mode (default: %d)\n", params.port);
+    fprintf(stderr, "  -m FNAME, --model FNAME\n                        model path (default: %s)\n\n", params.model);
+}
+extern "C" BERT_API bool bert_params_parse(int argc, char **argv, bert_params &params) {
+    for (int i = 1; i < argc; i++) {
+        const std::string arg = argv[i];
+        const bool has_next = i + 1 < argc;
+        if ((arg == "-t" || arg == "--threads") && has_next) params.n_threads = atoi(argv[++i]);
+        else if ((arg == "-p" || arg == "--prompt") && has_next) params.prompt = argv[++i];
+        else if (arg == "--port" && has_next) params.port = atoi(argv[++i]);
+        else if ((arg == "-m" || arg == "--model") && has_next) params.model = argv[++i];
+        else if (arg == "-h" || arg == "--help") { bert_print_usage(argv, params); exit(0); }
+        else { fprintf(stderr, "error: unknown argument: %s\n", arg.c_str()); bert_print_usage(argv, params); exit(0); }
+    }
+    return true;
+}

@@ -1,0 +1,490 @@
+// engine.cu -- one GPU's worth of the encoder: device weights, activation workspaces, the launch
+// sequence of one forward pass over a packed, variable-length batch, and the C ABI of include/bk_api.h.
+//
+// Replaces bert_build + ggml_graph_compute_with_ctx (bert.cpp:845-1012, 1077-1099; ggml.c:15961-16049):
+// the reference builds and walks a ~45-node-per-layer graph per sentence on CPU threads; here the plan
+// is static -- 2 + 7*n_layer + 2 kernel launches per batch on one CUDA stream.
+//
+// HBM layout (T = packed tokens of the launch, d = n_embd, f = n_intermediate; all activations f16):
+//   x   [T][d]   residual stream / LN output        xq  [T][d]  its Q8-rounded copy (Q4 models only)
+//   qkv [T][3d]  Q | K | V                          att [T][d]  attention output (Q8-rounded for Q4)
+//   pre [T][d]   GEMM epilogue output = Lin + bias + residual, input of add_ln
+//   y   [T][d]   post-attention LN output           yq  [T][d]  (Q4 models only)
+//   h   [T][f]   GELU(FF1) (Q8-rounded for Q4)
+// Weights: 2-D layer matrices as f16 [N][K] (K contiguous) -- the UMMA B operand; Q/K/V fused to one
+// [3d][d] matrix; embedding tables stay in their GGUF storage type and are decoded by the gather.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "../../include/bk_api.h"
+
+namespace bk {
+
+static thread_local std::string g_err;
+static int fail(const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return -1;
+}
+#define CK(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t _e = (call);                                                                  \
+        if (_e != cudaSuccess) return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+    } while (0)
+
+struct HostTensor {  // device copy of one GGUF tensor in its storage type
+    void *dev = nullptr;
+    int type = -1;
+    int64_t ne0 = 0, ne1 = 0;
+    size_t bytes = 0;
+};
+
+struct Layer {
+    __half *wqkv = nullptr, *wo = nullptr, *w1 = nullptr, *w2 = nullptr;
+    float *bqkv = nullptr;
+    const float *bo = nullptr, *b1 = nullptr, *b2 = nullptr, *ln1g = nullptr, *ln1b = nullptr, *ln2g = nullptr, *ln2b = nullptr;
+    CUtensorMap tm_wqkv, tm_wo, tm_w1, tm_w2;
+};
+
+static size_t tensor_bytes(int type, int64_t ne0, int64_t ne1) {
+    switch (type) {
+        case BK_F32: return (size_t)ne0 * ne1 * 4;
+        case BK_F16: return (size_t)ne0 * ne1 * 2;
+        case BK_Q4_0: return (size_t)(ne0 / 32) * 18 * ne1;
+        case BK_Q4_1: return (size_t)(ne0 / 32) * 20 * ne1;
+    }
+    return 0;
+}
+
+}  // namespace bk
+
+using namespace bk;
+
+struct bk_engine {
+    int device = 0;
+    bk_hparams hp{};
+    int cap_tokens = 0, cap_seqs = 0;
+    int num_sms = 148;
+    int qmode = 0;  // 0: F32/F16 weights; 1: Q4_0 (activations Q8_0-rounded); 2: Q4_1 (Q8_1)
+    cudaStream_t st = nullptr;
+    bool finalized = false;
+
+    std::vector<HostTensor> tens;
+    std::vector<Layer> layers;
+
+    // workspaces
+    int32_t *d_tokens = nullptr, *d_lens = nullptr, *d_cu = nullptr, *d_pos = nullptr;
+    __half *x = nullptr, *xq = nullptr, *qkv = nullptr, *att = nullptr, *pre = nullptr, *y = nullptr, *yq = nullptr, *h = nullptr;
+    float *d_out = nullptr;
+    CUtensorMap tm_x, tm_att, tm_y, tm_h;  // A-operand maps (x/y point at the Q8-rounded copy for Q4 models)
+    // pinned staging
+    int32_t *h_tokens = nullptr, *h_lens = nullptr;
+    float *h_out = nullptr;
+    // staged batch
+    int st_T = 0, st_nseq = 0, st_maxlen = 0;
+    // hidden-state capture (tests)
+    bool keep_hidden = false;
+    __half *hidden = nullptr;  // [n_layer+1][cap_tokens][d]
+    // timing
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> ev_kind;
+    bool timing = false;
+    float k_ms[BK_K_COUNT] = {0};
+    int k_launches[BK_K_COUNT] = {0};
+    int64_t launch_count = 0;
+};
+
+extern "C" {
+
+BK_API const char *bk_last_error(void) { return g_err.c_str(); }
+
+BK_API int bk_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { fail("cudaGetDeviceCount: %s", cudaGetErrorString(e)); return e == cudaErrorNoDevice ? 0 : -1; }
+    return n;
+}
+
+static int engine_alloc(bk_engine *e) {
+    const bk_hparams &hp = e->hp;
+    const size_t T = (size_t)e->cap_tokens, d = hp.n_embd, f = hp.n_intermediate;
+    CK(cudaMalloc(&e->d_tokens, T * 4));
+    CK(cudaMalloc(&e->d_pos, T * 4));
+    CK(cudaMalloc(&e->d_lens, (size_t)e->cap_seqs * 4));
+    CK(cudaMalloc(&e->d_cu, ((size_t)e->cap_seqs + 1) * 4));
+    CK(cudaMalloc(&e->x, T * d * 2));
+    CK(cudaMalloc(&e->qkv, T * 3 * d * 2));
+    CK(cudaMalloc(&e->att, T * d * 2));
+    CK(cudaMalloc(&e->pre, T * d * 2));
+    CK(cudaMalloc(&e->y, T * d * 2));
+    CK(cudaMalloc(&e->h, T * f * 2));
+    if (e->qmode) {
+        CK(cudaMalloc(&e->xq, T * d * 2));
+        CK(cudaMalloc(&e->yq, T * d * 2));
+    }
+    CK(cudaMalloc(&e->d_out, (size_t)e->cap_seqs * d * 4));
+    CK(cudaMallocHost(&e->h_tokens, T * 4));
+    CK(cudaMallocHost(&e->h_lens, (size_t)e->cap_seqs * 4));
+    CK(cudaMallocHost(&e->h_out, (size_t)e->cap_seqs * d * 4));
+    // the GEMM A operand may read (never store) rows past T inside the last 128-row tile: keep them finite
+    CK(cudaMemsetAsync(e->x, 0, T * d * 2, e->st));
+    CK(cudaMemsetAsync(e->att, 0, T * d * 2, e->st));
+    CK(cudaMemsetAsync(e->y, 0, T * d * 2, e->st));
+    CK(cudaMemsetAsync(e->h, 0, T * f * 2, e->st));
+    if (e->qmode) {
+        CK(cudaMemsetAsync(e->xq, 0, T * d * 2, e->st));
+        CK(cudaMemsetAsync(e->yq, 0, T * d * 2, e->st));
+    }
+    return 0;
+}
+
+BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap_tokens, int32_t cap_seqs) {
+    int n = bk_device_count();
+    if (n <= 0) { fail("no CUDA device available (this engine has no CPU path)"); return nullptr; }
+    if (device < 0 || device >= n) { fail("device %d out of range (have %d)", device, n); return nullptr; }
+    if (hp->n_embd % 32 || hp->n_intermediate % 32 || hp->n_embd % hp->n_head) { fail("unsupported shape: n_embd/n_intermediate must be multiples of 32"); return nullptr; }
+    const int dh = hp->n_embd / hp->n_head;
+    if (dh != 32 && dh != 64) { fail("unsupported head size %d (supported: 32, 64)", dh); return nullptr; }
+    if (hp->n_embd > 2048) { fail("unsupported n_embd %d (> 2048)", hp->n_embd); return nullptr; }
+    if (hp->wtype < BK_F32 || hp->wtype > BK_Q4_1) { fail("unsupported weight type %d", hp->wtype); return nullptr; }
+    if (cap_tokens < hp->n_max_tokens) cap_tokens = hp->n_max_tokens;
+    cap_tokens = (cap_tokens + 127) & ~127;
+    if (cap_seqs < 1) cap_seqs = 1;
+    if (cudaSetDevice(device) != cudaSuccess) { fail("cudaSetDevice(%d) failed", device); return nullptr; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { fail("cudaGetDeviceProperties failed"); return nullptr; }
+    if (prop.major != 10) { fail("device %d is sm_%d%d; this engine is built for sm_100a (B200) only", device, prop.major, prop.minor); return nullptr; }
+    bk_engine *e = new bk_engine();
+    e->device = device;
+    e->hp = *hp;
+    e->cap_tokens = cap_tokens;
+    e->cap_seqs = cap_seqs;
+    e->num_sms = prop.multiProcessorCount;
+    e->qmode = hp->wtype == BK_Q4_0 ? 1 : hp->wtype == BK_Q4_1 ? 2 : 0;
+    e->tens.resize(5 + 16 * (size_t)hp->n_layer);
+    e->layers.resize(hp->n_layer);
+    if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) { fail("cudaStreamCreate failed"); delete e; return nullptr; }
+    if (engine_alloc(e) != 0) { bk_engine_destroy(e); return nullptr; }
+    return e;
+}
+
+BK_API void bk_engine_destroy(bk_engine *e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->st) cudaStreamSynchronize(e->st);
+    for (auto &t : e->tens) if (t.dev) cudaFree(t.dev);
+    for (auto &l : e->layers) { cudaFree(l.wqkv); cudaFree(l.wo); cudaFree(l.w1); cudaFree(l.w2); cudaFree(l.bqkv); }
+    void *bufs[] = {e->d_tokens, e->d_lens, e->d_cu, e->d_pos, e->x, e->xq, e->qkv, e->att, e->pre, e->y, e->yq, e->h, e->d_out, e->hidden};
+    for (void *b : bufs) if (b) cudaFree(b);
+    if (e->h_tokens) cudaFreeHost(e->h_tokens);
+    if (e->h_lens) cudaFreeHost(e->h_lens);
+    if (e->h_out) cudaFreeHost(e->h_out);
+    for (auto ev : e->ev) cudaEventDestroy(ev);
+    if (e->st) cudaStreamDestroy(e->st);
+    delete e;
+}
+
+BK_API int bk_engine_set_tensor(bk_engine *e, int32_t slot, int32_t type, const void *data, int64_t ne0, int64_t ne1) {
+    if (!e || slot < 0 || slot >= (int)e->tens.size()) return fail("bad tensor slot %d", slot);
+    if (type < BK_F32 || type > BK_Q4_1) return fail("tensor slot %d: unsupported ggml type %d", slot, type);
+    if ((type == BK_Q4_0 || type == BK_Q4_1) && ne0 % 32) return fail("tensor slot %d: ne0 %lld not a multiple of 32", slot, (long long)ne0);
+    CK(cudaSetDevice(e->device));
+    HostTensor &t = e->tens[slot];
+    if (t.dev) { cudaFree(t.dev); t.dev = nullptr; }
+    t.type = type; t.ne0 = ne0; t.ne1 = ne1;
+    t.bytes = tensor_bytes(type, ne0, ne1);
+    CK(cudaMalloc(&t.dev, t.bytes));
+    CK(cudaMemcpy(t.dev, data, t.bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+// slot helpers (order of bert.cpp:623-652)
+static inline int L_SLOT(int layer, int k) { return 5 + 16 * layer + k; }
+enum { S_QW = 0, S_QB, S_KW, S_KB, S_VW, S_VB, S_OW, S_OB, S_LN1G, S_LN1B, S_W1, S_B1, S_W2, S_B2, S_LN2G, S_LN2B };
+
+static int expect(const bk_engine *e, int slot, int64_t ne0, int64_t ne1, bool must_f32, const char *what) {
+    const HostTensor &t = e->tens[slot];
+    if (!t.dev) return fail("tensor '%s' (slot %d) missing", what, slot);
+    if (t.ne0 != ne0 || t.ne1 != ne1) return fail("tensor '%s' has wrong shape: got {%lld,%lld}, expected {%lld,%lld}", what, (long long)t.ne0, (long long)t.ne1, (long long)ne0, (long long)ne1);
+    if (must_f32 && t.type != BK_F32) return fail("tensor '%s' must be F32", what);
+    return 0;
+}
+
+BK_API int bk_engine_finalize(bk_engine *e) {
+    if (!e) return fail("null engine");
+    CK(cudaSetDevice(e->device));
+    const bk_hparams &hp = e->hp;
+    const int64_t d = hp.n_embd, f = hp.n_intermediate;
+    if (expect(e, 0, d, hp.n_vocab, false, "embeddings.word_embeddings.weight")) return -1;
+    if (expect(e, 1, d, 2, false, "embeddings.token_type_embeddings.weight")) return -1;
+    if (expect(e, 2, d, hp.n_max_tokens, false, "embeddings.position_embeddings.weight")) return -1;
+    if (expect(e, 3, d, 1, true, "embeddings.LayerNorm.weight")) return -1;
+    if (expect(e, 4, d, 1, true, "embeddings.LayerNorm.bias")) return -1;
+    if (e->tens[0].type != e->tens[1].type || e->tens[0].type != e->tens[2].type) return fail("embedding tables have mixed types");
+    for (int l = 0; l < hp.n_layer; l++) {
+        Layer &L = e->layers[l];
+        const int wslots[4] = {S_QW, S_KW, S_VW, S_OW};
+        for (int k : wslots) if (expect(e, L_SLOT(l, k), d, d, false, "attention weight")) return -1;
+        const int bslots[8] = {S_QB, S_KB, S_VB, S_OB, S_LN1G, S_LN1B, S_LN2G, S_LN2B};
+        for (int k : bslots) if (expect(e, L_SLOT(l, k), d, 1, true, "bias / LayerNorm vector")) return -1;
+        if (expect(e, L_SLOT(l, S_W1), d, f, false, "intermediate.dense.weight")) return -1;
+        if (expect(e, L_SLOT(l, S_B1), f, 1, true, "intermediate.dense.bias")) return -1;
+        if (expect(e, L_SLOT(l, S_W2), f, d, false, "output.dense.weight")) return -1;
+        if (expect(e, L_SLOT(l, S_B2), d, 1, true, "output.dense.bias")) return -1;
+
+        CK(cudaMalloc(&L.wqkv, (size_t)3 * d * d * 2));
+        CK(cudaMalloc(&L.wo, (size_t)d * d * 2));
+        CK(cudaMalloc(&L.w1, (size_t)f * d * 2));
+        CK(cudaMalloc(&L.w2, (size_t)d * f * 2));
+        CK(cudaMalloc(&L.bqkv, (size_t)3 * d * 4));
+        const int qkvw[3] = {S_QW, S_KW, S_VW}, qkvb[3] = {S_QB, S_KB, S_VB};
+        for (int i = 0; i < 3; i++) {
+            const HostTensor &w = e->tens[L_SLOT(l, qkvw[i])];
+            CK(launch_weight_to_f16(w.dev, w.type, d, d, L.wqkv + (size_t)i * d * d, e->st));
+            CK(cudaMemcpyAsync(L.bqkv + (size_t)i * d, e->tens[L_SLOT(l, qkvb[i])].dev, (size_t)d * 4, cudaMemcpyDeviceToDevice, e->st));
+        }
+        { const HostTensor &w = e->tens[L_SLOT(l, S_OW)]; CK(launch_weight_to_f16(w.dev, w.type, d, d, L.wo, e->st)); }
+        { const HostTensor &w = e->tens[L_SLOT(l, S_W1)]; CK(launch_weight_to_f16(w.dev, w.type, f, d, L.w1, e->st)); }
+        { const HostTensor &w = e->tens[L_SLOT(l, S_W2)]; CK(launch_weight_to_f16(w.dev, w.type, d, f, L.w2, e->st)); }
+        L.bo = (const float *)e->tens[L_SLOT(l, S_OB)].dev;
+        L.b1 = (const float *)e->tens[L_SLOT(l, S_B1)].dev;
+        L.b2 = (const float *)e->tens[L_SLOT(l, S_B2)].dev;
+        L.ln1g = (const float *)e->tens[L_SLOT(l, S_LN1G)].dev;
+        L.ln1b = (const float *)e->tens[L_SLOT(l, S_LN1B)].dev;
+        L.ln2g = (const float *)e->tens[L_SLOT(l, S_LN2G)].dev;
+        L.ln2b = (const float *)e->tens[L_SLOT(l, S_LN2B)].dev;
+        bool ok = make_tmap_f16_2d(&L.tm_wqkv, L.wqkv, d, 3 * d, d * 2, GEMM_BLOCK_K, gemm_block_n(3 * (int)d)) &&
+                  make_tmap_f16_2d(&L.tm_wo, L.wo, d, d, d * 2, GEMM_BLOCK_K, gemm_block_n((int)d)) &&
+                  make_tmap_f16_2d(&L.tm_w1, L.w1, d, f, d * 2, GEMM_BLOCK_K, gemm_block_n((int)f)) &&
+                  make_tmap_f16_2d(&L.tm_w2, L.w2, f, d, f * 2, GEMM_BLOCK_K, gemm_block_n((int)d));
+        if (!ok) return fail("cuTensorMapEncodeTiled failed for layer %d weights", l);
+    }
+    CK(cudaStreamSynchronize(e->st));
+    // the packed 2-D layer weights are no longer needed on the device (only their f16 operand copies are)
+    for (int l = 0; l < hp.n_layer; l++) {
+        const int wslots[6] = {S_QW, S_KW, S_VW, S_OW, S_W1, S_W2};
+        for (int k : wslots) { HostTensor &t = e->tens[L_SLOT(l, k)]; cudaFree(t.dev); t.dev = nullptr; }
+    }
+    const uint64_t T = e->cap_tokens;
+    bool ok = make_tmap_f16_2d(&e->tm_x, e->qmode ? e->xq : e->x, d, T, d * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->tm_att, e->att, d, T, d * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->tm_y, e->qmode ? e->yq : e->y, d, T, d * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->tm_h, e->h, f, T, f * 2, GEMM_BLOCK_K, GEMM_BLOCK_M);
+    if (!ok) return fail("cuTensorMapEncodeTiled failed for activation buffers");
+    e->finalized = true;
+    return 0;
+}
+
+}  // extern "C"
+
+// =============================================================================== forward pass
+namespace {
+
+struct KTimer {  // brackets one kernel class with two events when timing is on
+    bk_engine *e;
+    int kind;
+    KTimer(bk_engine *e_, int kind_) : e(e_), kind(kind_) {
+        if (e->timing) push();
+    }
+    ~KTimer() {
+        if (e->timing) push();
+    }
+    void push() {
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        cudaEventRecord(ev, e->st);
+        e->ev.push_back(ev);
+        e->ev_kind.push_back(kind);
+    }
+};
+
+int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const CUtensorMap &tmB, int M, int N, int K, const float *bias,
+             const __half *resid, int ldr, __half *out, int ldo, int epi) {
+    KTimer t(e, kind);
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.bias = bias; p.resid = resid; p.ldr = ldr; p.out = out; p.ldo = ldo; p.epi = epi;
+    CK(launch_gemm(tmA, tmB, p, e->num_sms, e->st));
+    e->launch_count++;
+    return 0;
+}
+
+// all kernels of one batch already resident on the device (tokens, lens in d_tokens/d_lens)
+int forward_device(bk_engine *e, int T, int n_seq, int max_len) {
+    const bk_hparams &hp = e->hp;
+    const int d = hp.n_embd, f = hp.n_intermediate;
+    const int q = e->qmode;
+    {
+        KTimer t(e, BK_K_PACK);
+        CK(launch_pack(e->d_lens, n_seq, e->d_cu, e->d_pos, T, e->st));
+        e->launch_count += 2;
+    }
+    {
+        KTimer t(e, BK_K_EMBED_LN);
+        EmbedParams p;
+        p.word = e->tens[0].dev; p.type = e->tens[1].dev; p.posw = e->tens[2].dev; p.wtype = e->tens[0].type;
+        p.gamma = (const float *)e->tens[3].dev; p.beta = (const float *)e->tens[4].dev;
+        p.tokens = e->d_tokens; p.pos = e->d_pos; p.T = T; p.d = d; p.n_vocab = hp.n_vocab; p.eps = hp.eps;
+        p.x = e->x; p.xq = e->xq; p.qmode = q;
+        CK(launch_embed_ln(p, e->st));
+        e->launch_count++;
+    }
+    if (e->keep_hidden) CK(cudaMemcpyAsync(e->hidden, e->x, (size_t)T * d * 2, cudaMemcpyDeviceToDevice, e->st));
+    for (int l = 0; l < hp.n_layer; l++) {
+        Layer &L = e->layers[l];
+        if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, T, 3 * d, d, L.bqkv, nullptr, 0, e->qkv, 3 * d, BK_EPI_BIAS)) return -1;
+        {
+            KTimer t(e, BK_K_ATTN);
+            CK(launch_attention(e->qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
+            e->launch_count++;
+        }
+        if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, T, d, d, L.bo, e->x, d, e->pre, d, BK_EPI_BIAS_RESID)) return -1;
+        {
+            KTimer t(e, BK_K_ADD_LN);
+            CK(launch_add_ln(e->pre, L.ln1g, L.ln1b, T, d, hp.eps, e->y, e->yq, q, e->st));
+            e->launch_count++;
+        }
+        const int epi1 = q == 0 ? BK_EPI_BIAS_GELU : q == 1 ? BK_EPI_BIAS_GELU_Q8_0 : BK_EPI_BIAS_GELU_Q8_1;
+        if (run_gemm(e, BK_K_GEMM_FF1, e->tm_y, L.tm_w1, T, f, d, L.b1, nullptr, 0, e->h, f, epi1)) return -1;
+        if (run_gemm(e, BK_K_GEMM_FF2, e->tm_h, L.tm_w2, T, d, f, L.b2, e->y, d, e->pre, d, BK_EPI_BIAS_RESID)) return -1;
+        {
+            KTimer t(e, BK_K_ADD_LN);
+            CK(launch_add_ln(e->pre, L.ln2g, L.ln2b, T, d, hp.eps, e->x, e->xq, q, e->st));
+            e->launch_count++;
+        }
+        if (e->keep_hidden)
+            CK(cudaMemcpyAsync(e->hidden + (size_t)(l + 1) * e->cap_tokens * d, e->x, (size_t)T * d * 2, cudaMemcpyDeviceToDevice, e->st));
+    }
+    {
+        KTimer t(e, BK_K_POOL);
+        CK(launch_pool_norm(e->x, e->d_cu, n_seq, d, e->d_out, e->st));
+        e->launch_count++;
+    }
+    return 0;
+}
+
+int check_batch(bk_engine *e, const int32_t *lens, int n_seq, int *T_out, int *maxlen_out) {
+    if (!e || !e->finalized) return fail("engine not finalized");
+    if (n_seq < 1 || n_seq > e->cap_seqs) return fail("n_seq %d outside 1..%d", n_seq, e->cap_seqs);
+    long long T = 0;
+    int mx = 0;
+    for (int i = 0; i < n_seq; i++) {
+        if (lens[i] < 1 || lens[i] > e->hp.n_max_tokens) return fail("sentence %d has %d tokens (allowed 1..%d)", i, lens[i], e->hp.n_max_tokens);
+        T += lens[i];
+        if (lens[i] > mx) mx = lens[i];
+    }
+    if (T > e->cap_tokens) return fail("batch has %lld tokens, capacity %d", T, e->cap_tokens);
+    *T_out = (int)T;
+    *maxlen_out = mx;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq) {
+    int T, mx;
+    if (check_batch(e, lens, n_seq, &T, &mx)) return -1;
+    CK(cudaSetDevice(e->device));
+    memcpy(e->h_tokens, tokens, (size_t)T * 4);
+    memcpy(e->h_lens, lens, (size_t)n_seq * 4);
+    CK(cudaMemcpyAsync(e->d_tokens, e->h_tokens, (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
+    CK(cudaMemcpyAsync(e->d_lens, e->h_lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
+    CK(cudaStreamSynchronize(e->st));
+    e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
+    return 0;
+}
+
+BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq, float *out) {
+    int T, mx;
+    if (check_batch(e, lens, n_seq, &T, &mx)) return -1;
+    CK(cudaSetDevice(e->device));
+    memcpy(e->h_tokens, tokens, (size_t)T * 4);
+    memcpy(e->h_lens, lens, (size_t)n_seq * 4);
+    CK(cudaMemcpyAsync(e->d_tokens, e->h_tokens, (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
+    CK(cudaMemcpyAsync(e->d_lens, e->h_lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
+    e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
+    if (forward_device(e, T, n_seq, mx)) return -1;
+    const size_t ob = (size_t)n_seq * e->hp.n_embd * 4;
+    CK(cudaMemcpyAsync(e->h_out, e->d_out, ob, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));
+    memcpy(out, e->h_out, ob);
+    return 0;
+}
+
+BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernels, float *ms_total) {
+    if (!e || !e->finalized || e->st_T <= 0) return fail("nothing staged");
+    CK(cudaSetDevice(e->device));
+    for (auto ev : e->ev) cudaEventDestroy(ev);
+    e->ev.clear(); e->ev_kind.clear();
+    for (int k = 0; k < BK_K_COUNT; k++) { e->k_ms[k] = 0; e->k_launches[k] = 0; }
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    e->timing = time_kernels != 0;
+    CK(cudaEventRecord(a, e->st));
+    int rc = 0;
+    for (int i = 0; i < iters && rc == 0; i++) rc = forward_device(e, e->st_T, e->st_nseq, e->st_maxlen);
+    e->timing = false;
+    if (rc) { cudaEventDestroy(a); cudaEventDestroy(b); return rc; }
+    CK(cudaEventRecord(b, e->st));
+    CK(cudaStreamSynchronize(e->st));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, a, b));
+    if (ms_total) *ms_total = ms;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    for (size_t i = 0; i + 1 < e->ev.size(); i += 2) {
+        float t = 0;
+        cudaEventElapsedTime(&t, e->ev[i], e->ev[i + 1]);
+        e->k_ms[e->ev_kind[i]] += t;
+        e->k_launches[e->ev_kind[i]] += (e->ev_kind[i] == BK_K_PACK) ? 2 : 1;
+    }
+    for (auto ev : e->ev) cudaEventDestroy(ev);
+    e->ev.clear(); e->ev_kind.clear();
+    return 0;
+}
+
+BK_API int bk_engine_read_output(bk_engine *e, float *out, int32_t n_seq) {
+    if (!e || n_seq < 1 || n_seq > e->cap_seqs) return fail("bad n_seq");
+    CK(cudaSetDevice(e->device));
+    CK(cudaMemcpyAsync(out, e->d_out, (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));
+    return 0;
+}
+
+BK_API int bk_engine_kernel_ms(bk_engine *e, float *ms, int32_t *launches) {
+    if (!e) return fail("null engine");
+    for (int k = 0; k < BK_K_COUNT; k++) { if (ms) ms[k] = e->k_ms[k]; if (launches) launches[k] = e->k_launches[k]; }
+    return 0;
+}
+
+BK_API int bk_engine_set_keep_hidden(bk_engine *e, int32_t on) {
+    if (!e) return fail("null engine");
+    CK(cudaSetDevice(e->device));
+    if (on && !e->hidden) CK(cudaMalloc(&e->hidden, (size_t)(e->hp.n_layer + 1) * e->cap_tokens * e->hp.n_embd * 2));
+    e->keep_hidden = on != 0;
+    return 0;
+}
+
+BK_API int bk_engine_read_hidden(bk_engine *e, int32_t which, float *out) {
+    if (!e || !e->hidden || which < 0 || which > e->hp.n_layer) return fail("hidden state %d not captured", which);
+    CK(cudaSetDevice(e->device));
+    const size_t n = (size_t)e->st_T * e->hp.n_embd;
+    std::vector<__half> tmp(n);
+    CK(cudaMemcpy(tmp.data(), e->hidden + (size_t)which * e->cap_tokens * e->hp.n_embd, n * 2, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; i++) out[i] = __half2float(tmp[i]);
+    return 0;
+}
+
+BK_API int64_t bk_engine_launch_count(bk_engine *e) { return e ? e->launch_count : 0; }
+
+}  // extern "C"

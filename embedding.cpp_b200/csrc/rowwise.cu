@@ -1,0 +1,320 @@
+// rowwise.cu -- the HBM-bound kernels of the encoder, one warp per token row, warp-shuffle
+// reductions, 16-byte vector accesses:
+//   pack_kernel       on-device batcher tail: cu_seqlens (prefix sum of lengths) + per-token position
+//   embed_ln_kernel   gather(word,type,pos) + add + LayerNorm            (bert.cpp:868-898)
+//   add_ln_kernel     LayerNorm of the pre-LN sum the GEMM epilogue wrote (bert.cpp:958-963, 981-992)
+//   pool_norm_kernel  mean over the sentence's tokens + L2 normalise      (bert.cpp:995-1006)
+//   weight_to_f16     GGUF storage (F32/F16/Q4_0/Q4_1) -> f16 UMMA operand copy at load time
+// LayerNorm follows ggml_compute_forward_norm_f32 (ggml.c:8976-9004): two-pass mean / biased
+// variance, y = (x-mean) * (1/sqrtf(var+eps)), then *gamma, +beta as separate roundings.
+// For Q4 models the LN output is also written Q8_0/Q8_1-rounded per 32 elements (what
+// quantize_row_q8_0/1 feed the reference's integer dot products, ggml-quants.c:702-747, 944-985).
+#include "common.cuh"
+#include "kernels.h"
+#include "../../include/bk_api.h"
+
+namespace bk {
+
+constexpr int kMaxChunks = 8;  // 8 halves per chunk, 32 lanes -> d <= 2048
+
+// ------------------------------------------------------------------------------------- pack
+// lens[n_seq] -> cu[n_seq+1]; pos[t] = t - cu[seq(t)].  Single CTA scan (n_seq is at most a few
+// thousand per launch), then all CTAs fill positions by binary search over cu.
+__global__ void pack_scan_kernel(const int32_t *__restrict__ lens, int n_seq, int32_t *__restrict__ cu) {
+    __shared__ int32_t warp_tot[32];
+    __shared__ int32_t carry_s;
+    if (threadIdx.x == 0) { carry_s = 0; cu[0] = 0; }
+    __syncthreads();
+    for (int base = 0; base < n_seq; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        int v = (i < n_seq) ? lens[i] : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int n = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((int)lane_id() >= o) incl += n;
+        }
+        if (lane_id() == 31) warp_tot[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            int w = (threadIdx.x < (blockDim.x >> 5)) ? warp_tot[threadIdx.x] : 0;
+            int wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int n = __shfl_up_sync(0xffffffffu, wi, o);
+                if ((int)lane_id() >= o) wi += n;
+            }
+            warp_tot[threadIdx.x] = wi - w;  // exclusive warp offsets
+        }
+        __syncthreads();
+        const int tot = incl + warp_tot[threadIdx.x >> 5] + carry_s;
+        if (i < n_seq) cu[i + 1] = tot;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry_s = tot;
+        __syncthreads();
+    }
+}
+__global__ void pack_pos_kernel(const int32_t *__restrict__ cu, int n_seq, int32_t *__restrict__ pos, int T) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= T) return;
+    int lo = 0, hi = n_seq;  // find s with cu[s] <= t < cu[s+1]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(cu + mid) <= t) lo = mid; else hi = mid;
+    }
+    pos[t] = t - __ldg(cu + lo);
+}
+cudaError_t launch_pack(const int32_t *lens, int n_seq, int32_t *cu_seqlens, int32_t *pos, int T, cudaStream_t st) {
+    pack_scan_kernel<<<1, 1024, 0, st>>>(lens, n_seq, cu_seqlens);
+    pack_pos_kernel<<<(T + 255) / 256, 256, 0, st>>>(cu_seqlens, n_seq, pos, T);
+    return cudaGetLastError();
+}
+
+// ----------------------------------------------------------------------- table row decoding
+// 8 consecutive elements [8c, 8c+8) of row `r` of a [rows][d] table in GGUF storage
+// (ggml_compute_forward_get_rows_*, ggml.c:10108-10224; Q4 decode ggml-quants.c:1074-1113).
+__device__ __forceinline__ void load_row8(const void *tab, int wtype, int64_t r, int d, int c, float (&v)[8]) {
+    if (wtype == BK_F16) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(tab) + r * d) + c);
+        float2 f;
+        f = unpack_h2(u.x); v[0] = f.x; v[1] = f.y;
+        f = unpack_h2(u.y); v[2] = f.x; v[3] = f.y;
+        f = unpack_h2(u.z); v[4] = f.x; v[5] = f.y;
+        f = unpack_h2(u.w); v[6] = f.x; v[7] = f.y;
+    } else if (wtype == BK_F32) {
+        const float4 *p = reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(tab) + r * d) + 2 * c;
+        const float4 a = __ldg(p), b = __ldg(p + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+        // block of 32 = f16 d (+ f16 m for Q4_1) + 16 bytes; element j<16 low nibble of byte j, j+16 high nibble
+        const int bb = (wtype == BK_Q4_0) ? 18 : 20;
+        const int blk = c >> 2, o = (c & 3) * 8;
+        const uint8_t *bp = reinterpret_cast<const uint8_t *>(tab) + (r * (d >> 5) + blk) * bb;
+        const uint16_t *hp = reinterpret_cast<const uint16_t *>(bp);  // blocks are 2-byte aligned
+        const float dd = __half2float(__ushort_as_half(__ldg(hp)));
+        const float mm = (wtype == BK_Q4_1) ? __half2float(__ushort_as_half(__ldg(hp + 1))) : 0.f;
+        const uint16_t *qp = reinterpret_cast<const uint16_t *>(bp + (bb - 16) + (o & 15));
+        const int sh = (o >= 16) ? 4 : 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t w = __ldg(qp + j);
+            const int q0 = (w >> sh) & 0xF, q1 = (w >> (8 + sh)) & 0xF;
+            if (wtype == BK_Q4_0) { v[2 * j] = (float)(q0 - 8) * dd; v[2 * j + 1] = (float)(q1 - 8) * dd; }
+            else { v[2 * j] = (float)q0 * dd + mm; v[2 * j + 1] = (float)q1 * dd + mm; }
+        }
+    }
+}
+
+// --------------------------------------------------------------- LN core on registers (one warp)
+// v[it][8] holds chunk c = lane + 32*it of the row (valid iff c < d/8).
+template <bool kWriteQ>
+__device__ __forceinline__ void ln_store(float (&v)[kMaxChunks][8], int d, float eps, const float *__restrict__ gamma,
+                                         const float *__restrict__ beta, __half *__restrict__ y, __half *__restrict__ yq, int qmode) {
+    const int lane = lane_id();
+    const int nch = d >> 3;
+    float s = 0.f;
+#pragma unroll
+    for (int it = 0; it < kMaxChunks; it++)
+        if (lane + 32 * it < nch)
+#pragma unroll
+            for (int j = 0; j < 8; j++) s += v[it][j];
+    const float mean = warp_sum(s) / (float)d;
+    float s2 = 0.f;
+#pragma unroll
+    for (int it = 0; it < kMaxChunks; it++)
+        if (lane + 32 * it < nch)
+#pragma unroll
+            for (int j = 0; j < 8; j++) { const float t = v[it][j] - mean; v[it][j] = t; s2 += t * t; }
+    const float var = warp_sum(s2) / (float)d;
+    const float scale = 1.0f / sqrtf(var + eps);
+#pragma unroll
+    for (int it = 0; it < kMaxChunks; it++) {
+        const int c = lane + 32 * it;
+        const bool ok = c < nch;
+        float o[8];
+        if (ok) {
+            const float4 g0 = __ldg(reinterpret_cast<const float4 *>(gamma) + 2 * c), g1 = __ldg(reinterpret_cast<const float4 *>(gamma) + 2 * c + 1);
+            const float4 b0 = __ldg(reinterpret_cast<const float4 *>(beta) + 2 * c), b1 = __ldg(reinterpret_cast<const float4 *>(beta) + 2 * c + 1);
+            const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int j = 0; j < 8; j++) o[j] = __fadd_rn(__fmul_rn(g[j], __fmul_rn(v[it][j], scale)), b[j]);  // three roundings: norm, ggml_mul, ggml_add
+            uint4 u;
+            u.x = pack_h2(o[0], o[1]); u.y = pack_h2(o[2], o[3]); u.z = pack_h2(o[4], o[5]); u.w = pack_h2(o[6], o[7]);
+            reinterpret_cast<uint4 *>(y)[c] = u;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; j++) o[j] = 0.f;
+        }
+        if (kWriteQ) {
+            // one Q8 block = 32 elements = chunks 4b..4b+3 = four adjacent lanes of this iteration
+            float amax = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; j++) amax = fmaxf(amax, fabsf(o[j]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            if (ok) {
+                float id, dq;
+                q8_scales(amax, qmode, id, dq);
+                uint4 u;
+                u.x = pack_h2(q8_round(o[0], id, dq), q8_round(o[1], id, dq));
+                u.y = pack_h2(q8_round(o[2], id, dq), q8_round(o[3], id, dq));
+                u.z = pack_h2(q8_round(o[4], id, dq), q8_round(o[5], id, dq));
+                u.w = pack_h2(q8_round(o[6], id, dq), q8_round(o[7], id, dq));
+                reinterpret_cast<uint4 *>(yq)[c] = u;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------- embed + LN
+template <bool kWriteQ>
+__global__ void __launch_bounds__(256) embed_ln_kernel(const EmbedParams p) {
+    const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (t >= p.T) return;
+    const int lane = lane_id();
+    const int nch = p.d >> 3;
+    int tok = __ldg(p.tokens + t);
+    tok = min(max(tok, 0), p.n_vocab - 1);
+    const int ps = __ldg(p.pos + t);
+    float v[kMaxChunks][8];
+#pragma unroll
+    for (int it = 0; it < kMaxChunks; it++) {
+        const int c = lane + 32 * it;
+        if (c < nch) {
+            float w[8], ty[8], po[8];
+            load_row8(p.word, p.wtype, tok, p.d, c, w);
+            load_row8(p.type, p.wtype, 0, p.d, c, ty);   // token type is always 0 (bert.cpp:871-872)
+            load_row8(p.posw, p.wtype, ps, p.d, c, po);
+#pragma unroll
+            for (int j = 0; j < 8; j++) { const float a = ty[j] + w[j]; v[it][j] = po[j] + a; }  // (type + word) + pos, bert.cpp:880-887
+        }
+    }
+    ln_store<kWriteQ>(v, p.d, p.eps, p.gamma, p.beta, p.x + (size_t)t * p.d, kWriteQ ? p.xq + (size_t)t * p.d : nullptr, p.qmode);
+}
+cudaError_t launch_embed_ln(const EmbedParams &p, cudaStream_t st) {
+    if (p.d % 32 != 0 || p.d > kMaxChunks * 256) return cudaErrorInvalidValue;
+    const int wpb = 8;
+    const int grid = (p.T + wpb - 1) / wpb;
+    if (p.qmode) embed_ln_kernel<true><<<grid, wpb * 32, 0, st>>>(p);
+    else embed_ln_kernel<false><<<grid, wpb * 32, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+// --------------------------------------------------------------------------------- add + LN
+template <bool kWriteQ>
+__global__ void __launch_bounds__(256) add_ln_kernel(const __half *__restrict__ pre, const float *__restrict__ gamma,
+                                                     const float *__restrict__ beta, int T, int d, float eps,
+                                                     __half *__restrict__ y, __half *__restrict__ yq, int qmode) {
+    const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (t >= T) return;
+    const int lane = lane_id();
+    const int nch = d >> 3;
+    const uint4 *src = reinterpret_cast<const uint4 *>(pre + (size_t)t * d);
+    float v[kMaxChunks][8];
+    uint4 u[kMaxChunks];
+#pragma unroll
+    for (int it = 0; it < kMaxChunks; it++)
+        if (lane + 32 * it < nch) u[it] = __ldg(src + lane + 32 * it);
+#pragma unroll
+    for (int it = 0; it < kMaxChunks; it++)
+        if (lane + 32 * it < nch) {
+            float2 f;
+            f = unpack_h2(u[it].x); v[it][0] = f.x; v[it][1] = f.y;
+            f = unpack_h2(u[it].y); v[it][2] = f.x; v[it][3] = f.y;
+            f = unpack_h2(u[it].z); v[it][4] = f.x; v[it][5] = f.y;
+            f = unpack_h2(u[it].w); v[it][6] = f.x; v[it][7] = f.y;
+        }
+    ln_store<kWriteQ>(v, d, eps, gamma, beta, y + (size_t)t * d, kWriteQ ? yq + (size_t)t * d : nullptr, qmode);
+}
+cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *beta, int T, int d, float eps, __half *y,
+                          __half *yq, int qmode, cudaStream_t st) {
+    if (d % 32 != 0 || d > kMaxChunks * 256) return cudaErrorInvalidValue;
+    const int wpb = 8;
+    const int grid = (T + wpb - 1) / wpb;
+    if (qmode) add_ln_kernel<true><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, qmode);
+    else add_ln_kernel<false><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, 0);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------ mean-pool + L2 norm
+// One CTA per sentence.  e[k] = sum_t x[t][k] * (1/L) (the reference multiplies by a vector of 1/L,
+// bert.cpp:999-1001), out = e * (1/sqrt(sum e^2)) (bert.cpp:1004-1006).
+__global__ void __launch_bounds__(256) pool_norm_kernel(const __half *__restrict__ x, const int32_t *__restrict__ cu,
+                                                        int d, float *__restrict__ out) {
+    extern __shared__ float sacc[];  // [ngroups][d]
+    __shared__ float red[8];
+    const int s = blockIdx.x;
+    const int t0 = __ldg(cu + s), t1 = __ldg(cu + s + 1);
+    const int L = t1 - t0;
+    const int nch = d >> 3;
+    // thread layout: column-chunk c = threadIdx.x % cpr, row group g = threadIdx.x / cpr
+    const int cpr = nch < 256 ? nch : 256;  // chunks handled per pass
+    const int groups = 256 / cpr > 0 ? 256 / cpr : 1;
+    const int g = threadIdx.x / cpr, c0 = threadIdx.x % cpr;
+    const float invL = 1.0f / (float)L;
+    for (int c = c0; c < nch; c += cpr) {
+        float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (g < groups) {
+            for (int t = t0 + g; t < t1; t += groups) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4 *>(x + (size_t)t * d) + c);
+                float2 f;
+                f = unpack_h2(u.x); a[0] = fmaf(f.x, invL, a[0]); a[1] = fmaf(f.y, invL, a[1]);
+                f = unpack_h2(u.y); a[2] = fmaf(f.x, invL, a[2]); a[3] = fmaf(f.y, invL, a[3]);
+                f = unpack_h2(u.z); a[4] = fmaf(f.x, invL, a[4]); a[5] = fmaf(f.y, invL, a[5]);
+                f = unpack_h2(u.w); a[6] = fmaf(f.x, invL, a[6]); a[7] = fmaf(f.y, invL, a[7]);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; j++) sacc[(size_t)g * d + c * 8 + j] = a[j];
+        }
+    }
+    __syncthreads();
+    float ss = 0.f;
+    for (int k = threadIdx.x; k < d; k += blockDim.x) {
+        float e = 0.f;
+        for (int gg = 0; gg < groups; gg++) e += sacc[(size_t)gg * d + k];
+        sacc[k] = e;  // group 0 slot now holds the mean (each k is touched by one thread only)
+        ss += e * e;
+    }
+    ss = warp_sum(ss);
+    if (lane_id() == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; w++) tot += red[w];
+    const float inv = 1.0f / sqrtf(tot);
+    for (int k = threadIdx.x; k < d; k += blockDim.x) out[(size_t)s * d + k] = sacc[k] * inv;
+}
+cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, int n_seq, int d, float *out, cudaStream_t st) {
+    if (d % 8 != 0) return cudaErrorInvalidValue;
+    const int nch = d >> 3;
+    const int cpr = nch < 256 ? nch : 256;
+    const int groups = 256 / cpr > 0 ? 256 / cpr : 1;
+    const size_t smem = (size_t)groups * d * sizeof(float);
+    pool_norm_kernel<<<n_seq, 256, smem, st>>>(x, cu_seqlens, d, out);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------- weight storage -> f16
+__global__ void weight_to_f16_kernel(const void *__restrict__ src, int wtype, int64_t rows, int K, __half *__restrict__ dst) {
+    const int64_t nch = rows * (int64_t)(K >> 3);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nch; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / (K >> 3);
+        const int c = (int)(i % (K >> 3));
+        float v[8];
+        load_row8(src, wtype, r, K, c, v);
+        uint4 u;
+        u.x = pack_h2(v[0], v[1]); u.y = pack_h2(v[2], v[3]); u.z = pack_h2(v[4], v[5]); u.w = pack_h2(v[6], v[7]);
+        reinterpret_cast<uint4 *>(dst)[i] = u;
+    }
+}
+cudaError_t launch_weight_to_f16(const void *src, int wtype, int64_t rows, int64_t K, __half *dst, cudaStream_t st) {
+    if (K % 32 != 0) return cudaErrorInvalidValue;
+    const int64_t nch = rows * (K >> 3);
+    int grid = (int)((nch + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    weight_to_f16_kernel<<<grid, 256, 0, st>>>(src, wtype, rows, (int)K, dst);
+    return cudaGetLastError();
+}
+
+}  // namespace bk

@@ -1,0 +1,126 @@
+// test_entry.cu -- single-kernel C-ABI entry points (include/bk_api.h, bk_test_*): host buffers in,
+// one kernel on the device, host buffers out.  Used by tests/ (parity per kernel against oracle/) and
+// for isolated ncu captures; the product path (engine.cu) launches the same kernels directly.
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "../../include/bk_api.h"
+
+using namespace bk;
+
+namespace {
+thread_local std::string t_err;
+struct DevBuf {
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
+    template <class T> T *as() { return reinterpret_cast<T *>(p); }
+};
+#define TCK(call)                                                                                       \
+    do {                                                                                                \
+        cudaError_t _e = (call);                                                                        \
+        if (_e != cudaSuccess) { fprintf(stderr, "bk_test: %s:%d %s: %s\n", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); return -1; } \
+    } while (0)
+
+int upload_lens(const int32_t *lens, int n_seq, DevBuf &d_lens, DevBuf &d_cu, DevBuf &d_pos, int *T_out, int *max_out, cudaStream_t st) {
+    int T = 0, mx = 0;
+    for (int i = 0; i < n_seq; i++) { T += lens[i]; if (lens[i] > mx) mx = lens[i]; }
+    TCK(d_lens.alloc((size_t)n_seq * 4));
+    TCK(d_cu.alloc(((size_t)n_seq + 1) * 4));
+    TCK(d_pos.alloc((size_t)T * 4));
+    TCK(cudaMemcpy(d_lens.p, lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice));
+    TCK(launch_pack(d_lens.as<int32_t>(), n_seq, d_cu.as<int32_t>(), d_pos.as<int32_t>(), T, st));
+    *T_out = T; *max_out = mx;
+    return 0;
+}
+}  // namespace
+
+extern "C" {
+
+BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint16_t *A, const void *W, int32_t wtype,
+                        const float *bias, const uint16_t *resid, int32_t epi, uint16_t *out, float *ms) {
+    TCK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    TCK(cudaGetDeviceProperties(&prop, device));
+    size_t wbytes = wtype == BK_F32 ? (size_t)N * K * 4 : wtype == BK_F16 ? (size_t)N * K * 2 : (size_t)N * (K / 32) * (wtype == BK_Q4_0 ? 18 : 20);
+    DevBuf dA, dWraw, dW, dB, dR, dO;
+    TCK(dA.alloc((size_t)M * K * 2)); TCK(dWraw.alloc(wbytes)); TCK(dW.alloc((size_t)N * K * 2));
+    TCK(dB.alloc((size_t)N * 4)); TCK(dR.alloc((size_t)M * N * 2)); TCK(dO.alloc((size_t)M * N * 2));
+    TCK(cudaMemcpy(dA.p, A, (size_t)M * K * 2, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dWraw.p, W, wbytes, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dB.p, bias, (size_t)N * 4, cudaMemcpyHostToDevice));
+    if (resid) TCK(cudaMemcpy(dR.p, resid, (size_t)M * N * 2, cudaMemcpyHostToDevice));
+    TCK(cudaMemset(dO.p, 0xFF, (size_t)M * N * 2));
+    TCK(launch_weight_to_f16(dWraw.p, wtype, N, K, dW.as<__half>(), 0));
+    CUtensorMap tmA, tmB;
+    if (!make_tmap_f16_2d(&tmA, dA.p, K, M, (uint64_t)K * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) ||
+        !make_tmap_f16_2d(&tmB, dW.p, K, N, (uint64_t)K * 2, GEMM_BLOCK_K, gemm_block_n(N))) {
+        fprintf(stderr, "bk_test_gemm: cuTensorMapEncodeTiled failed\n");
+        return -1;
+    }
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.bias = dB.as<float>(); p.resid = resid ? dR.as<__half>() : nullptr; p.ldr = N;
+    p.out = dO.as<__half>(); p.ldo = N; p.epi = epi;
+    cudaEvent_t a, b;
+    TCK(cudaEventCreate(&a)); TCK(cudaEventCreate(&b));
+    TCK(launch_gemm(tmA, tmB, p, prop.multiProcessorCount, 0));  // warm-up (also first-use setup)
+    TCK(cudaDeviceSynchronize());
+    const int reps = ms ? 5 : 1;
+    TCK(cudaEventRecord(a, 0));
+    for (int i = 0; i < reps; i++) TCK(launch_gemm(tmA, tmB, p, prop.multiProcessorCount, 0));
+    TCK(cudaEventRecord(b, 0));
+    TCK(cudaDeviceSynchronize());
+    float t = 0;
+    TCK(cudaEventElapsedTime(&t, a, b));
+    if (ms) *ms = t / reps;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    TCK(cudaMemcpy(out, dO.p, (size_t)M * N * 2, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+BK_API int bk_test_add_ln(int device, int32_t T, int32_t d, float eps, const uint16_t *pre, const float *gamma,
+                          const float *beta, int32_t qmode, uint16_t *y, uint16_t *yq) {
+    TCK(cudaSetDevice(device));
+    DevBuf dP, dG, dB, dY, dQ;
+    TCK(dP.alloc((size_t)T * d * 2)); TCK(dG.alloc((size_t)d * 4)); TCK(dB.alloc((size_t)d * 4));
+    TCK(dY.alloc((size_t)T * d * 2)); TCK(dQ.alloc((size_t)T * d * 2));
+    TCK(cudaMemcpy(dP.p, pre, (size_t)T * d * 2, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dG.p, gamma, (size_t)d * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dB.p, beta, (size_t)d * 4, cudaMemcpyHostToDevice));
+    TCK(launch_add_ln(dP.as<__half>(), dG.as<float>(), dB.as<float>(), T, d, eps, dY.as<__half>(), dQ.as<__half>(), qmode, 0));
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(y, dY.p, (size_t)T * d * 2, cudaMemcpyDeviceToHost));
+    if (qmode && yq) TCK(cudaMemcpy(yq, dQ.p, (size_t)T * d * 2, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+BK_API int bk_test_attention(int device, int32_t n_seq, const int32_t *lens, int32_t d, int32_t n_head,
+                             const uint16_t *qkv, int32_t qmode, uint16_t *out) {
+    TCK(cudaSetDevice(device));
+    DevBuf dL, dC, dPos, dQ, dO;
+    int T, mx;
+    if (upload_lens(lens, n_seq, dL, dC, dPos, &T, &mx, 0)) return -1;
+    TCK(dQ.alloc((size_t)T * 3 * d * 2)); TCK(dO.alloc((size_t)T * d * 2));
+    TCK(cudaMemcpy(dQ.p, qkv, (size_t)T * 3 * d * 2, cudaMemcpyHostToDevice));
+    TCK(launch_attention(dQ.as<__half>(), dC.as<int32_t>(), n_seq, mx, d, n_head, dO.as<__half>(), qmode, 0));
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(out, dO.p, (size_t)T * d * 2, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t d, const uint16_t *x, float *out) {
+    TCK(cudaSetDevice(device));
+    DevBuf dL, dC, dPos, dX, dO;
+    int T, mx;
+    if (upload_lens(lens, n_seq, dL, dC, dPos, &T, &mx, 0)) return -1;
+    TCK(dX.alloc((size_t)T * d * 2)); TCK(dO.alloc((size_t)n_seq * d * 4));
+    TCK(cudaMemcpy(dX.p, x, (size_t)T * d * 2, cudaMemcpyHostToDevice));
+    TCK(launch_pool_norm(dX.as<__half>(), dC.as<int32_t>(), n_seq, d, dO.as<float>(), 0));
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(out, dO.p, (size_t)n_seq * d * 4, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+}  // extern "C"

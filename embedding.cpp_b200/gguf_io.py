@@ -153,6 +153,7 @@ SHAPES = {  # name -> BertHParams overrides (BASELINE.json configs)
     # small shapes for CPU-side tests (same structure, seconds on the oracle)
     "tiny": dict(n_embd=64, n_intermediate=128, n_head=2, n_layer=2, n_max_tokens=64),
     "mini": dict(n_embd=128, n_intermediate=512, n_head=4, n_layer=2, n_max_tokens=512),
+    "mini64": dict(n_embd=256, n_intermediate=1024, n_head=4, n_layer=2, n_max_tokens=512),  # head size 64
 }
 
 

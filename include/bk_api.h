@@ -1,0 +1,100 @@
+/*
+ * include/bk_api.h -- the thin C ABI between the C++ host layer (api.cpp, host.cpp) and the
+ * sm_100a CUDA engine (engine.cu + kernels).  Plain pointers and sizes only.
+ *
+ * One bk_engine = one GPU: device weights, activation workspaces, one stream.  The bert.h layer
+ * (include/bert.h) owns one engine per GPU and shards a batch of independent sentences over them
+ * (reference loop bert.cpp:1065 has no cross-sentence state).
+ *
+ * What each call replaces in the reference is cited per function.  There is no CPU fallback: every
+ * function fails (non-zero return, message via bk_last_error()) when no CUDA device is usable.
+ */
+#ifndef BK_API_H
+#define BK_API_H
+
+#include <stdint.h>
+
+#define BK_API __attribute__((visibility("default")))
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ggml_type ids as stored in GGUF (ggml.h:310-313) */
+enum { BK_F32 = 0, BK_F16 = 1, BK_Q4_0 = 2, BK_Q4_1 = 3 };
+
+/* bert_hparams, bert.cpp:20-31 */
+typedef struct bk_hparams {
+    int32_t n_vocab, n_max_tokens, n_embd, n_intermediate, n_head, n_layer;
+    float   eps;
+    int32_t wtype; /* file type = type of the 2-D weights (BK_F32..BK_Q4_1), bert.cpp:206-252 */
+} bk_hparams;
+
+/* kernel classes, for per-kernel timing (bk_engine_kernel_ms) */
+enum {
+    BK_K_PACK = 0, BK_K_EMBED_LN, BK_K_GEMM_QKV, BK_K_ATTN, BK_K_GEMM_O, BK_K_ADD_LN,
+    BK_K_GEMM_FF1, BK_K_GEMM_FF2, BK_K_POOL, BK_K_COUNT
+};
+
+typedef struct bk_engine bk_engine;
+
+BK_API int         bk_device_count(void);          /* <0 on CUDA error, 0 = no device */
+BK_API const char *bk_last_error(void);            /* thread-local message of the last failure */
+
+/* Replaces the compute arena + ggml context of bert_ctx (bert.cpp:80-137, 821-842): workspaces
+ * for up to cap_tokens packed tokens / cap_seqs sentences per launch are allocated once. */
+BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap_tokens, int32_t cap_seqs);
+BK_API void       bk_engine_destroy(bk_engine *e);
+
+/* Replaces llm_load_tensors/load_all_data (bert.cpp:580-658): `slot` indexes the canonical
+ * tensor order of bert.cpp:623-652 (0 word, 1 type, 2 pos, 3 ln_e.w, 4 ln_e.b, then 16 per layer:
+ * q.w q.b k.w k.b v.w v.b o.w o.b ln_att.w ln_att.b ff_i.w ff_i.b ff_o.w ff_o.b ln_out.w ln_out.b).
+ * `data` are the raw GGUF bytes of the tensor (host); ne0 = contiguous dim. */
+BK_API int bk_engine_set_tensor(bk_engine *e, int32_t slot, int32_t ggml_type, const void *data,
+                                int64_t ne0, int64_t ne1);
+/* after all tensors: builds the fused QKV weight/bias, UMMA operand copies and TMA descriptors */
+BK_API int bk_engine_finalize(bk_engine *e);
+
+/* Replaces one pass of the bert_eval_batch loop body (bert.cpp:1065-1099) for n_seq sentences:
+ * tokens = the sentences' ids concatenated (host), lens[n_seq] their lengths (host, each
+ * 1..n_max_tokens, sum <= cap_tokens), out = n_seq rows of n_embd floats (host).
+ * H2D copy, all kernels and the D2H copy run on the engine's stream; returns after it drained. */
+BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq, float *out);
+
+/* Same work with the inputs already resident in HBM (bench.py `value` leg): stage once, then run
+ * the kernels `iters` times, timed with CUDA events on the engine's stream.
+ * ms_total = elapsed ms for all iters; per-kernel-class ms via bk_engine_kernel_ms(). */
+BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq);
+BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernels, float *ms_total);
+BK_API int bk_engine_read_output(bk_engine *e, float *out, int32_t n_seq);
+/* ms[BK_K_COUNT], launches[BK_K_COUNT]: accumulated over the last bk_engine_run_staged(time_kernels=1) */
+BK_API int bk_engine_kernel_ms(bk_engine *e, float *ms, int32_t *launches);
+/* intermediate activations of the last forward, widened to f32 (tests): which = 0 embeddings+LN
+ * output, 1..n_layer = output of that encoder layer; out[T][n_embd] */
+BK_API int bk_engine_read_hidden(bk_engine *e, int32_t which, float *out);
+BK_API int bk_engine_set_keep_hidden(bk_engine *e, int32_t on);
+BK_API int64_t bk_engine_launch_count(bk_engine *e); /* kernels launched since creation */
+
+/* ---- single-kernel entry points (tests/, profiles): host buffers in, host buffers out --------
+ * f16 buffers are raw IEEE binary16 bit patterns (uint16_t). */
+enum { BK_EPI_BIAS = 0, BK_EPI_BIAS_RESID = 1, BK_EPI_BIAS_GELU = 2, BK_EPI_BIAS_GELU_Q8_0 = 3, BK_EPI_BIAS_GELU_Q8_1 = 4 };
+/* out[M][N] = epi(A[M][K] . W[N][K]^T + bias[N] (+ resid[M][N]))   -- ggml_mul_mat + bias add,
+ * ggml.c:9388-9597, bert.cpp:909-910.  wtype selects how W is stored (BK_F16 raw halves,
+ * BK_Q4_0/BK_Q4_1 GGUF blocks along K, BK_F32 floats). */
+BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint16_t *A, const void *W,
+                        int32_t wtype, const float *bias, const uint16_t *resid, int32_t epi,
+                        uint16_t *out, float *ms);
+/* LN(x)*gamma+beta over rows of `pre` (f16) -> y f16 (+ yq = Q8-rounded copy when qmode 1=Q8_0, 2=Q8_1);
+ * ggml_norm + mul + add, ggml.c:8976-9004, bert.cpp:958-963 */
+BK_API int bk_test_add_ln(int device, int32_t T, int32_t d, float eps, const uint16_t *pre, const float *gamma,
+                          const float *beta, int32_t qmode, uint16_t *y, uint16_t *yq);
+/* softmax(Q.K^T/sqrt(dh)).V per sentence and head on packed qkv[T][3d] (f16); bert.cpp:928-943 */
+BK_API int bk_test_attention(int device, int32_t n_seq, const int32_t *lens, int32_t d, int32_t n_head,
+                             const uint16_t *qkv, int32_t qmode, uint16_t *out);
+/* mean over tokens + L2 normalise; bert.cpp:995-1006 */
+BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t d, const uint16_t *x, float *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BK_API_H */

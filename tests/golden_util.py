@@ -1,0 +1,22 @@
+"""Loading the committed golden cases (tests/golden/*.npz, made by tests/golden/gen_golden.py)."""
+import glob
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def golden_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(HERE, "golden", "*.npz")))
+
+
+def load_golden(name):
+    z = np.load(os.path.join(HERE, "golden", name + ".npz"))
+    lens = z["lens"]
+    toks, off = [], 0
+    for L in lens:
+        toks.append(z["tokens"][off:off + L].astype(np.int32))
+        off += L
+    return dict(shape=str(z["shape"]), ftype=str(z["ftype"]), seed=int(z["seed"]), n_vocab=int(z["n_vocab"]),
+                dist=str(z["dist"]), tokens=toks, emb=z["emb"])

@@ -1,0 +1,121 @@
+"""GPU: the whole path through the reference-facing C API (bert_eval / bert_eval_batch in
+build/libbert.so) against (a) the committed outputs of the reference itself (tests/golden) and
+(b) the oracle on fresh seeded inputs.  Gate (BASELINE.json north_star): per-sentence cosine >= 0.9999
+and max-abs <= 1e-3 on the normalised embeddings for F32/F16; cosine >= 0.9999 for Q4_0/Q4_1."""
+import numpy as np
+import pytest
+
+from conftest import cos_maxabs, rand_tokens
+from golden_util import golden_names, load_golden
+
+pytestmark = pytest.mark.gpu
+
+COS_MIN = 0.9999
+MAXABS = 1e-3
+
+
+def check(got, want, ftype, what, stress=False):
+    c, m = cos_maxabs(got, want)
+    assert abs(float(np.linalg.norm(got)) - 1.0) < 1e-3, what
+    if stress and ftype.startswith("q4"):
+        # reported, not gating (SURVEY.md finding 4: Q8 activation rounding is chaotic at sigma = 0.1)
+        assert c >= 0.999, (what, c, m)
+        return c, m
+    assert c >= COS_MIN, (what, c, m)
+    if not ftype.startswith("q4"):
+        assert m <= MAXABS, (what, c, m)
+    return c, m
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_matches_reference_golden(name, binding, make_model):
+    c = load_golden(name)
+    path = make_model(c["shape"], c["ftype"], c["seed"], c["n_vocab"], c["dist"])
+    m = binding.BertB200(path)
+    stress = c["dist"] == "stress"
+    # one sentence per call (bert_eval) ...
+    for t, e in zip(c["tokens"], c["emb"]):
+        check(m.eval(t), e, c["ftype"], f"{name} L={len(t)} bert_eval", stress)
+    # ... and all of them as one ragged batch (bert_eval_batch): same answers, any order
+    out = m.eval_batch(c["tokens"])
+    for t, e, g in zip(c["tokens"], c["emb"], out):
+        check(g, e, c["ftype"], f"{name} L={len(t)} bert_eval_batch", stress)
+    m.close()
+
+
+@pytest.mark.parametrize("ftype", ["f32", "f16", "q4_0", "q4_1"])
+@pytest.mark.parametrize("shape", ["mini", "mini64"])
+def test_ragged_batch_vs_oracle(shape, ftype, binding, orc, make_model):
+    path = make_model(shape, ftype, seed=41)
+    o = orc.Oracle(path)
+    m = binding.BertB200(path)
+    rng = np.random.default_rng(17)
+    lens = [1, 2, 3, 16, 31, 32, 33, 64, 100, 128, 129, 255, 384, 512] + list(rng.integers(1, 200, 50))
+    batch = [rand_tokens(rng, 500, int(L)) for L in lens]
+    got = m.eval_batch(batch)
+    worst = (1.0, 0.0)
+    for t, g in zip(batch, got):
+        c, mx = check(g, o.eval(t), ftype, f"{shape} {ftype} L={len(t)}")
+        worst = (min(worst[0], c), max(worst[1], mx))
+    print(f"\n{shape} {ftype}: worst cos {worst[0]:.7f} max-abs {worst[1]:.2e} over {len(batch)} sentences")
+    m.close()
+
+
+def test_batch_equals_single_and_is_deterministic(binding, make_model):
+    path = make_model("mini", "f16", seed=41)
+    m = binding.BertB200(path)
+    rng = np.random.default_rng(3)
+    batch = [rand_tokens(rng, 500, int(L)) for L in rng.integers(1, 300, 40)]
+    a = m.eval_batch(batch)
+    b = m.eval_batch(batch[::-1])[::-1]
+    assert np.array_equal(a, b)          # order / packing position does not change a sentence's result
+    for i in (0, 7, 39):
+        assert np.array_equal(a[i], m.eval(batch[i]))
+    m.close()
+
+
+def test_hidden_states_vs_oracle(binding, orc, make_model):
+    """per-layer intermediates: localises an error to a layer instead of only seeing the pooled output"""
+    path = make_model("mini64", "f16", seed=41)
+    o = orc.Oracle(path)
+    e = binding.Engine(path, cap_tokens=1024, cap_seqs=16)
+    e.keep_hidden(True)
+    rng = np.random.default_rng(8)
+    toks = rand_tokens(rng, 500, 77)
+    out = e.forward([toks])
+    ref, layers = o.eval(toks, layers=True)
+    for l in range(layers.shape[0]):
+        got = e.hidden(l, len(toks))
+        assert np.allclose(got, layers[l], rtol=5e-3, atol=5e-3), (l, float(np.abs(got - layers[l]).max()))
+    c, mx = cos_maxabs(out[0], ref)
+    assert c >= COS_MIN and mx <= MAXABS
+    assert e.launch_count() == 2 + 1 + 7 * e.hp.n_layer + 1
+    e.close()
+
+
+def test_error_behaviour(binding, make_model):
+    """bert.cpp:1071-1075: too many tokens -> message on stderr, outputs untouched; NULL embeddings tolerated"""
+    path = make_model("tiny", "f32", 13, 300)
+    m = binding.BertB200(path)
+    assert m.n_max_tokens == 64 and m.n_embd == 64
+    out = m.eval_batch([np.arange(65, dtype=np.int32) % 300, np.arange(5, dtype=np.int32)])
+    assert not out.any()
+    m.lib.bert_eval(m.ctx, 1, np.arange(4, dtype=np.int32).ctypes.data_as(binding._i32p), 4, None)
+    assert m.lib.bert_vocab_id_to_token(m.ctx, 101) == b"[CLS]"
+    m.close()
+
+
+def test_large_batch_properties(binding, make_model):
+    """full-size shape at a size the CPU oracle cannot cover: unit norm, permutation invariance, duplicates equal"""
+    path = make_model("minilm-l6", "q4_0", 14, 1000)
+    m = binding.BertB200(path)
+    rng = np.random.default_rng(5)
+    base = [rand_tokens(rng, 1000, 128) for _ in range(256)]
+    batch = base + base[:64]
+    out = m.eval_batch(batch)
+    assert np.allclose(np.linalg.norm(out, axis=1), 1.0, atol=1e-3)
+    assert np.array_equal(out[:64], out[256:])
+    perm = rng.permutation(len(batch))
+    out2 = m.eval_batch([batch[i] for i in perm])
+    assert np.array_equal(out2, out[perm])
+    m.close()

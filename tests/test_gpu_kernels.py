@@ -1,0 +1,160 @@
+"""GPU: each sm_100a kernel alone through its C-ABI test entry (bk_test_*), against NumPy / oracle/."""
+import ctypes
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+_u16p = ctypes.POINTER(ctypes.c_uint16)
+_f32p = ctypes.POINTER(ctypes.c_float)
+_i32p = ctypes.POINTER(ctypes.c_int32)
+
+
+def h(a):
+    return np.ascontiguousarray(a, dtype=np.float16)
+
+
+def u16(a):
+    return a.view(np.uint16).ctypes.data_as(_u16p)
+
+
+def gelu16(orc_lib, x):
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.zeros_like(x)
+    orc_lib.oracle_gelu(x.size, x.ctypes.data_as(_f32p), y.ctypes.data_as(_f32p))
+    return y
+
+
+def run_gemm(lib, A, Wraw, wtype, N, bias, resid, epi, want_ms=False):
+    M, K = A.shape
+    out = np.zeros((M, N), np.float16)
+    ms = ctypes.c_float(0)
+    rc = lib.bk_test_gemm(0, M, N, K, u16(A), Wraw.ctypes.data, wtype, bias.ctypes.data_as(_f32p),
+                          u16(resid) if resid is not None else None, epi, u16(out), ctypes.byref(ms) if want_ms else None)
+    assert rc == 0
+    return out, ms.value
+
+
+GEMM_SHAPES = [(128, 256, 64), (128, 128, 128), (77, 64, 128), (300, 384, 384), (1000, 2304, 768), (515, 768, 3072),
+               (4096, 3072, 768), (129, 1152, 384)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+@pytest.mark.parametrize("epi", [0, 1, 2])
+def test_gemm_f16_weights(lib, binding, orc, make_model, M, N, K, epi):
+    rng = np.random.default_rng(M * 7 + N * 3 + K + epi)
+    A = h(rng.standard_normal((M, K)) * 0.5)
+    W = h(rng.standard_normal((N, K)) * 0.05)
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float32)
+    resid = h(rng.standard_normal((M, N))) if epi == 1 else None
+    out, _ = run_gemm(lib, A, W, binding.BK_F16, N, bias, resid, epi)
+    ref = A.astype(np.float32) @ W.astype(np.float32).T + bias
+    if epi == 1:
+        ref = ref + resid.astype(np.float32)
+    if epi == 2:
+        o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+        ref = gelu16(o.lib, ref)
+    err = np.abs(out.astype(np.float32) - ref)
+    tol = 2e-3 * np.abs(ref) + 2e-3
+    if epi == 2:  # a 1-ulp f16 difference of the GELU input can move the output by one f16 ulp
+        assert (err <= tol).mean() > 0.999 and err.max() < 2e-2
+    else:
+        assert (err <= tol).all(), (float(err.max()), np.unravel_index(err.argmax(), err.shape))
+
+
+@pytest.mark.parametrize("wname,wtype", [("q4_0", 2), ("q4_1", 3), ("f32", 0)])
+def test_gemm_other_weight_storage(lib, gio, wname, wtype):
+    """Q4_0/Q4_1/F32 weight storage: the product decodes GGUF blocks itself; compare with the NumPy decode."""
+    M, N, K = 200, 384, 768
+    rng = np.random.default_rng(3)
+    A = h(rng.standard_normal((M, K)) * 0.5)
+    Wf = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    if wtype == 0:
+        raw, Wd = Wf, Wf.astype(np.float16).astype(np.float32)  # F32 weights are used as f16 operands
+    else:
+        raw = (gio.quantize_q4_0 if wtype == 2 else gio.quantize_q4_1)(Wf)
+        Wd = gio.dequantize(raw, wtype, (N, K)).astype(np.float16).astype(np.float32)
+    bias = np.zeros(N, np.float32)
+    out, _ = run_gemm(lib, A, np.ascontiguousarray(raw), wtype, N, bias, None, 0)
+    ref = A.astype(np.float32) @ Wd.T
+    err = np.abs(out.astype(np.float32) - ref)
+    assert (err <= 2e-3 * np.abs(ref) + 2e-3).all(), float(err.max())
+
+
+@pytest.mark.parametrize("qepi,fn", [(3, "oracle_quant_q8_0_roundtrip"), (4, "oracle_quant_q8_1_roundtrip")])
+def test_gemm_gelu_q8_epilogue(lib, binding, orc, make_model, qepi, fn):
+    M, N, K = 256, 512, 128
+    rng = np.random.default_rng(9)
+    A = h(rng.standard_normal((M, K)) * 0.5)
+    W = h(rng.standard_normal((N, K)) * 0.1)
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float32)
+    plain, _ = run_gemm(lib, A, W, binding.BK_F16, N, bias, None, 2)
+    q, _ = run_gemm(lib, A, W, binding.BK_F16, N, bias, None, qepi)
+    o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+    src = np.ascontiguousarray(plain.astype(np.float32))
+    want = np.zeros_like(src)
+    getattr(o.lib, fn)(src.ctypes.data_as(_f32p), want.ctypes.data_as(_f32p), src.size)
+    # the kernel quantises the same f16-valued GELU outputs -> same integers; only the final f16 store rounds
+    assert np.allclose(q.astype(np.float32), want, rtol=1e-3, atol=1e-6)
+
+
+@pytest.mark.parametrize("T,d", [(1, 64), (37, 128), (1000, 384), (513, 768), (300, 1024)])
+@pytest.mark.parametrize("qmode", [0, 1, 2])
+def test_add_ln(lib, orc, make_model, T, d, qmode):
+    rng = np.random.default_rng(T + d)
+    pre = h(rng.standard_normal((T, d)) * 2 + 0.3)
+    gamma = (1 + 0.1 * rng.standard_normal(d)).astype(np.float32)
+    beta = (0.1 * rng.standard_normal(d)).astype(np.float32)
+    y = np.zeros((T, d), np.float16)
+    yq = np.zeros((T, d), np.float16)
+    assert lib.bk_test_add_ln(0, T, d, 1e-12, u16(pre), gamma.ctypes.data_as(_f32p), beta.ctypes.data_as(_f32p), qmode, u16(y), u16(yq)) == 0
+    o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+    o.hp.eps = 1e-12
+    ref = o.layernorm(pre.astype(np.float32), gamma, beta)
+    assert np.allclose(y.astype(np.float32), ref, rtol=1e-3, atol=1e-3)
+    if qmode:
+        want = np.zeros_like(ref)
+        fn = o.lib.oracle_quant_q8_0_roundtrip if qmode == 1 else o.lib.oracle_quant_q8_1_roundtrip
+        fn(ref.ctypes.data_as(_f32p), want.ctypes.data_as(_f32p), ref.size)
+        err = np.abs(yq.astype(np.float32) - want)
+        step = np.abs(ref).reshape(T, d // 32, 32).max(-1, keepdims=True) / 127.0
+        step = np.broadcast_to(step, (T, d // 32, 32)).reshape(T, d)
+        # fp32-vs-double LN sums can flip a rounding decision for values sitting on a .5 boundary
+        assert (err <= 1e-3 * np.abs(want) + 1e-6).mean() > 0.995
+        assert (err <= step * 1.01 + 1e-3).all()
+
+
+@pytest.mark.parametrize("d,H,lens", [(128, 4, [5, 128, 1, 33]), (256, 4, [64, 17, 200]), (768, 12, [128, 128, 16]),
+                                      (384, 12, [512, 2]), (256, 4, [512, 300, 129])])
+def test_attention(lib, orc, make_model, d, H, lens):
+    rng = np.random.default_rng(d + sum(lens))
+    T = sum(lens)
+    qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
+    out = np.zeros((T, d), np.float16)
+    L = np.array(lens, np.int32)
+    assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), 0, u16(out)) == 0
+    o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+    off = 0
+    for n in lens:
+        blk = qkv[off:off + n].astype(np.float32)
+        ref = o.attention(blk[:, :d], blk[:, d:2 * d], blk[:, 2 * d:], H)
+        got = out[off:off + n].astype(np.float32)
+        assert np.allclose(got, ref, rtol=2e-3, atol=2e-3), (n, float(np.abs(got - ref).max()))
+        off += n
+
+
+@pytest.mark.parametrize("d,lens", [(64, [1, 2, 64]), (384, [128, 7]), (768, [128] * 5 + [512]), (1024, [33])])
+def test_pool_norm(lib, orc, make_model, d, lens):
+    rng = np.random.default_rng(d)
+    T = sum(lens)
+    x = h(rng.standard_normal((T, d)))
+    out = np.zeros((len(lens), d), np.float32)
+    L = np.array(lens, np.int32)
+    assert lib.bk_test_pool(0, len(lens), L.ctypes.data_as(_i32p), d, u16(x), out.ctypes.data_as(_f32p)) == 0
+    o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+    off = 0
+    for i, n in enumerate(lens):
+        ref = o.pool(x[off:off + n].astype(np.float32))
+        assert np.allclose(out[i], ref, rtol=1e-5, atol=1e-6)
+        off += n
