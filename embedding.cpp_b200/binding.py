@@ -28,8 +28,9 @@ BERT_SYMBOLS = ["bert_load_from_file", "bert_free", "bert_encode", "bert_encode_
                 "bert_params_parse"]
 BK_SYMBOLS = ["bk_device_count", "bk_last_error", "bk_engine_create", "bk_engine_destroy", "bk_engine_set_tensor",
               "bk_engine_finalize", "bk_engine_forward", "bk_engine_stage", "bk_engine_run_staged", "bk_engine_read_output",
-              "bk_engine_kernel_ms", "bk_engine_read_hidden", "bk_engine_set_keep_hidden", "bk_engine_launch_count",
-              "bk_test_gemm", "bk_test_add_ln", "bk_test_attention", "bk_test_pool"]
+              "bk_engine_kernel_ms", "bk_engine_read_hidden", "bk_engine_set_keep_hidden", "bk_engine_launch_count", "bk_profiler_range",
+              "bk_test_gemm", "bk_test_add_ln", "bk_test_attention", "bk_test_pool",
+              "bk_tokenizer_create", "bk_tokenizer_destroy", "bk_tokenizer_encode"]
 
 
 class bk_hparams(ctypes.Structure):
@@ -92,13 +93,42 @@ def load_library(path: str | None = None):
     L.bk_engine_set_keep_hidden.argtypes = [vp, i32]
     L.bk_engine_launch_count.restype = i64
     L.bk_engine_launch_count.argtypes = [vp]
+    L.bk_profiler_range.argtypes = [i32]
     L.bk_test_gemm.argtypes = [ctypes.c_int, i32, i32, i32, _u16p, vp, i32, _f32p, _u16p, i32, _u16p, _f32p]
     L.bk_test_add_ln.argtypes = [ctypes.c_int, i32, i32, ctypes.c_float, _u16p, _f32p, _f32p, i32, _u16p, _u16p]
     L.bk_test_attention.argtypes = [ctypes.c_int, i32, _i32p, i32, i32, _u16p, i32, _u16p]
     L.bk_test_pool.argtypes = [ctypes.c_int, i32, _i32p, i32, _u16p, _f32p]
+    L.bk_tokenizer_create.restype = vp
+    L.bk_tokenizer_create.argtypes = [ctypes.c_char_p, i64]
+    L.bk_tokenizer_destroy.restype = None
+    L.bk_tokenizer_destroy.argtypes = [vp]
+    L.bk_tokenizer_encode.restype = i32
+    L.bk_tokenizer_encode.argtypes = [vp, ctypes.c_char_p, _i32p, i32]
     if path is None:
         _lib = L
     return L
+
+
+class Tokenizer:
+    """The C++ WordPiece tokenizer alone (host only)."""
+
+    def __init__(self, tokenizer_json: str, lib=None):
+        self.lib = lib or load_library()
+        b = tokenizer_json.encode("utf-8")
+        self.t = self.lib.bk_tokenizer_create(b, len(b))
+        if not self.t:
+            raise RuntimeError("bk_tokenizer_create failed")
+
+    def encode(self, text: str):
+        buf = np.zeros(max(16, 4 * len(text) + 16), np.int32)
+        n = self.lib.bk_tokenizer_encode(self.t, text.encode("utf-8"), _ptr(buf, _i32p), len(buf))
+        assert 0 <= n <= len(buf)
+        return buf[:n].tolist()
+
+    def close(self):
+        if self.t:
+            self.lib.bk_tokenizer_destroy(self.t)
+            self.t = None
 
 
 def _ptr(a: np.ndarray, t):

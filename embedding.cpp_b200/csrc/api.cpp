@@ -286,6 +286,23 @@ BERT_API void bert_encode(struct bert_ctx *ctx, int32_t n_threads, const char *t
 
 }  // extern "C"
 
+struct bk_tokenizer { WordPieceTokenizer tok; };
+extern "C" {
+BK_API bk_tokenizer *bk_tokenizer_create(const char *json, int64_t json_len) {
+    std::unique_ptr<bk_tokenizer> t(new bk_tokenizer());
+    std::string err;
+    if (!t->tok.load(std::string(json, (size_t)json_len), err)) { fprintf(stderr, "bk_tokenizer_create: %s\n", err.c_str()); return nullptr; }
+    return t.release();
+}
+BK_API void bk_tokenizer_destroy(bk_tokenizer *t) { delete t; }
+BK_API int32_t bk_tokenizer_encode(const bk_tokenizer *t, const char *text, int32_t *ids, int32_t max_ids) {
+    if (!t || !text) return -1;
+    const std::vector<int32_t> v = t->tok.encode(text);
+    for (int32_t i = 0; i < (int32_t)v.size() && i < max_ids; i++) ids[i] = v[i];
+    return (int32_t)v.size();
+}
+}
+
 // bert.cpp:681-733
 static void bert_print_usage(char **argv, const bert_params &params) {
     fprintf(stderr, "usage: %s [options]\n\noptions:\n", argv[0]);

@@ -20,6 +20,8 @@
 #include <string>
 #include <vector>
 
+#include <cuda_profiler_api.h>
+
 #include "kernels.h"
 #include "../../include/bk_api.h"
 
@@ -90,7 +92,14 @@ struct bk_engine {
     int32_t *h_tokens = nullptr, *h_lens = nullptr;
     float *h_out = nullptr;
     // staged batch
-    int st_T = 0, st_nseq = 0, st_maxlen = 0;
+    int st_T = 0, st_nseq = 0, st_maxlen = 0;  // last forward (hidden-state readback)
+    // staged set (bench `value` leg): a whole job resident in HBM, cut into micro-batches of <= cap_tokens
+    struct Slice { int tok_off, seq_off, T, n_seq, max_len; };
+    std::vector<Slice> slices;
+    int32_t *sg_tokens = nullptr, *sg_lens = nullptr;
+    float *sg_out = nullptr;
+    size_t sg_cap_tokens = 0, sg_cap_seqs = 0;
+    int sg_nseq = 0;
     // hidden-state capture (tests)
     bool keep_hidden = false;
     __half *hidden = nullptr;  // [n_layer+1][cap_tokens][d]
@@ -183,7 +192,7 @@ BK_API void bk_engine_destroy(bk_engine *e) {
     if (e->st) cudaStreamSynchronize(e->st);
     for (auto &t : e->tens) if (t.dev) cudaFree(t.dev);
     for (auto &l : e->layers) { cudaFree(l.wqkv); cudaFree(l.wo); cudaFree(l.w1); cudaFree(l.w2); cudaFree(l.bqkv); }
-    void *bufs[] = {e->d_tokens, e->d_lens, e->d_cu, e->d_pos, e->x, e->xq, e->qkv, e->att, e->pre, e->y, e->yq, e->h, e->d_out, e->hidden};
+    void *bufs[] = {e->d_tokens, e->d_lens, e->d_cu, e->d_pos, e->x, e->xq, e->qkv, e->att, e->pre, e->y, e->yq, e->h, e->d_out, e->hidden, e->sg_tokens, e->sg_lens, e->sg_out};
     for (void *b : bufs) if (b) cudaFree(b);
     if (e->h_tokens) cudaFreeHost(e->h_tokens);
     if (e->h_lens) cudaFreeHost(e->h_lens);
@@ -318,13 +327,13 @@ int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const CUtensorMap &
 }
 
 // all kernels of one batch already resident on the device (tokens, lens in d_tokens/d_lens)
-int forward_device(bk_engine *e, int T, int n_seq, int max_len) {
+int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens, int T, int n_seq, int max_len, float *d_out) {
     const bk_hparams &hp = e->hp;
     const int d = hp.n_embd, f = hp.n_intermediate;
     const int q = e->qmode;
     {
         KTimer t(e, BK_K_PACK);
-        CK(launch_pack(e->d_lens, n_seq, e->d_cu, e->d_pos, T, e->st));
+        CK(launch_pack(d_lens, n_seq, e->d_cu, e->d_pos, T, e->st));
         e->launch_count += 2;
     }
     {
@@ -332,7 +341,7 @@ int forward_device(bk_engine *e, int T, int n_seq, int max_len) {
         EmbedParams p;
         p.word = e->tens[0].dev; p.type = e->tens[1].dev; p.posw = e->tens[2].dev; p.wtype = e->tens[0].type;
         p.gamma = (const float *)e->tens[3].dev; p.beta = (const float *)e->tens[4].dev;
-        p.tokens = e->d_tokens; p.pos = e->d_pos; p.T = T; p.d = d; p.n_vocab = hp.n_vocab; p.eps = hp.eps;
+        p.tokens = d_tokens; p.pos = e->d_pos; p.T = T; p.d = d; p.n_vocab = hp.n_vocab; p.eps = hp.eps;
         p.x = e->x; p.xq = e->xq; p.qmode = q;
         CK(launch_embed_ln(p, e->st));
         e->launch_count++;
@@ -365,7 +374,7 @@ int forward_device(bk_engine *e, int T, int n_seq, int max_len) {
     }
     {
         KTimer t(e, BK_K_POOL);
-        CK(launch_pool_norm(e->x, e->d_cu, n_seq, d, e->d_out, e->st));
+        CK(launch_pool_norm(e->x, e->d_cu, n_seq, d, d_out, e->st));
         e->launch_count++;
     }
     return 0;
@@ -392,15 +401,36 @@ int check_batch(bk_engine *e, const int32_t *lens, int n_seq, int *T_out, int *m
 extern "C" {
 
 BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq) {
-    int T, mx;
-    if (check_batch(e, lens, n_seq, &T, &mx)) return -1;
+    if (!e || !e->finalized) return fail("engine not finalized");
+    if (n_seq < 1) return fail("n_seq %d < 1", n_seq);
     CK(cudaSetDevice(e->device));
-    memcpy(e->h_tokens, tokens, (size_t)T * 4);
-    memcpy(e->h_lens, lens, (size_t)n_seq * 4);
-    CK(cudaMemcpyAsync(e->d_tokens, e->h_tokens, (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
-    CK(cudaMemcpyAsync(e->d_lens, e->h_lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
+    // cut the job into micro-batches in the given order (callers sort by length, as bert_eval_batch does)
+    e->slices.clear();
+    long long total = 0;
+    for (int i = 0; i < n_seq;) {
+        bk_engine::Slice sl{(int)total, i, 0, 0, 0};
+        while (i < n_seq && sl.n_seq < e->cap_seqs) {
+            if (lens[i] < 1 || lens[i] > e->hp.n_max_tokens) return fail("sentence %d has %d tokens (allowed 1..%d)", i, lens[i], e->hp.n_max_tokens);
+            if (sl.T + lens[i] > e->cap_tokens) break;
+            sl.T += lens[i]; sl.n_seq++;
+            if (lens[i] > sl.max_len) sl.max_len = lens[i];
+            i++;
+        }
+        total += sl.T;
+        e->slices.push_back(sl);
+    }
+    if ((size_t)total > e->sg_cap_tokens || (size_t)n_seq > e->sg_cap_seqs) {
+        cudaFree(e->sg_tokens); cudaFree(e->sg_lens); cudaFree(e->sg_out);
+        e->sg_tokens = e->sg_lens = nullptr; e->sg_out = nullptr;
+        CK(cudaMalloc(&e->sg_tokens, (size_t)total * 4));
+        CK(cudaMalloc(&e->sg_lens, (size_t)n_seq * 4));
+        CK(cudaMalloc(&e->sg_out, (size_t)n_seq * e->hp.n_embd * 4));
+        e->sg_cap_tokens = (size_t)total; e->sg_cap_seqs = (size_t)n_seq;
+    }
+    CK(cudaMemcpyAsync(e->sg_tokens, tokens, (size_t)total * 4, cudaMemcpyHostToDevice, e->st));
+    CK(cudaMemcpyAsync(e->sg_lens, lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
     CK(cudaStreamSynchronize(e->st));
-    e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
+    e->sg_nseq = n_seq;
     return 0;
 }
 
@@ -413,7 +443,7 @@ BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t 
     CK(cudaMemcpyAsync(e->d_tokens, e->h_tokens, (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
     CK(cudaMemcpyAsync(e->d_lens, e->h_lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
     e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
-    if (forward_device(e, T, n_seq, mx)) return -1;
+    if (forward_device(e, e->d_tokens, e->d_lens, T, n_seq, mx, e->d_out)) return -1;
     const size_t ob = (size_t)n_seq * e->hp.n_embd * 4;
     CK(cudaMemcpyAsync(e->h_out, e->d_out, ob, cudaMemcpyDeviceToHost, e->st));
     CK(cudaStreamSynchronize(e->st));
@@ -422,7 +452,7 @@ BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t 
 }
 
 BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernels, float *ms_total) {
-    if (!e || !e->finalized || e->st_T <= 0) return fail("nothing staged");
+    if (!e || !e->finalized || e->slices.empty()) return fail("nothing staged");
     CK(cudaSetDevice(e->device));
     for (auto ev : e->ev) cudaEventDestroy(ev);
     e->ev.clear(); e->ev_kind.clear();
@@ -433,7 +463,13 @@ BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernel
     e->timing = time_kernels != 0;
     CK(cudaEventRecord(a, e->st));
     int rc = 0;
-    for (int i = 0; i < iters && rc == 0; i++) rc = forward_device(e, e->st_T, e->st_nseq, e->st_maxlen);
+    for (int i = 0; i < iters && rc == 0; i++)
+        for (const auto &sl : e->slices) {
+            e->st_T = sl.T; e->st_nseq = sl.n_seq; e->st_maxlen = sl.max_len;
+            rc = forward_device(e, e->sg_tokens + sl.tok_off, e->sg_lens + sl.seq_off, sl.T, sl.n_seq, sl.max_len,
+                                e->sg_out + (size_t)sl.seq_off * e->hp.n_embd);
+            if (rc) break;
+        }
     e->timing = false;
     if (rc) { cudaEventDestroy(a); cudaEventDestroy(b); return rc; }
     CK(cudaEventRecord(b, e->st));
@@ -454,9 +490,9 @@ BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernel
 }
 
 BK_API int bk_engine_read_output(bk_engine *e, float *out, int32_t n_seq) {
-    if (!e || n_seq < 1 || n_seq > e->cap_seqs) return fail("bad n_seq");
+    if (!e || n_seq < 1 || n_seq > e->sg_nseq) return fail("bad n_seq");
     CK(cudaSetDevice(e->device));
-    CK(cudaMemcpyAsync(out, e->d_out, (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaMemcpyAsync(out, e->sg_out, (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
     CK(cudaStreamSynchronize(e->st));
     return 0;
 }
@@ -486,5 +522,10 @@ BK_API int bk_engine_read_hidden(bk_engine *e, int32_t which, float *out) {
 }
 
 BK_API int64_t bk_engine_launch_count(bk_engine *e) { return e ? e->launch_count : 0; }
+
+BK_API int bk_profiler_range(int32_t on) {
+    CK(on ? cudaProfilerStart() : cudaProfilerStop());
+    return 0;
+}
 
 }  // extern "C"

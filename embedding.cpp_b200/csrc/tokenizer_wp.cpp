@@ -257,3 +257,158 @@ std::string encode_utf8(const uint32_t *b, const uint32_t *e) {
 }
 
 }  // namespace
+
+// =============================================================================== tokenizer
+bool WordPieceTokenizer::load(const std::string &json, std::string &err) {
+    JParser jp{json.data(), json.data() + json.size(), {}};
+    JValue root;
+    if (!jp.value(root) || root.kind != JValue::Obj) { err = "tokenizer.json: " + (jp.err.empty() ? std::string("not an object") : jp.err); return false; }
+    const JValue *model = root.get("model");
+    if (!model || model->kind != JValue::Obj) { err = "tokenizer.json: no model section"; return false; }
+    const JValue *type = model->get("type");
+    const JValue *vocab = model->get("vocab");
+    if (type && type->kind == JValue::Str && type->str != "WordPiece") { err = "tokenizer model '" + type->str + "' is not WordPiece"; return false; }
+    if (!vocab || vocab->kind != JValue::Obj) { err = "tokenizer.json: model.vocab missing"; return false; }
+    vocab_.reserve(vocab->obj.size() * 2);
+    for (const auto &kv : vocab->obj) vocab_[kv.first] = (int32_t)kv.second.num;
+    if (const JValue *v = model->get("unk_token")) if (v->kind == JValue::Str) unk_token_ = v->str;
+    if (const JValue *v = model->get("continuing_subword_prefix")) if (v->kind == JValue::Str) prefix_ = v->str;
+    if (const JValue *v = model->get("max_input_chars_per_word")) if (v->kind == JValue::Num) max_chars_ = (int)v->num;
+    auto it = vocab_.find(unk_token_);
+    if (it == vocab_.end()) { err = "unk_token '" + unk_token_ + "' not in vocab"; return false; }
+    unk_id_ = it->second;
+
+    const JValue *norm = root.get("normalizer");
+    has_normalizer_ = norm && norm->kind == JValue::Obj;
+    if (has_normalizer_) {
+        const JValue *t = norm->get("type");
+        if (!t || t->kind != JValue::Str || t->str != "BertNormalizer") { err = "normalizer type not supported (only BertNormalizer)"; return false; }
+        auto flag = [&](const char *k, bool dflt) { const JValue *v = norm->get(k); return (v && v->kind == JValue::Bool) ? v->b : dflt; };
+        clean_text_ = flag("clean_text", true);
+        chinese_ = flag("handle_chinese_chars", true);
+        lowercase_ = flag("lowercase", true);
+        const JValue *sa = norm->get("strip_accents");
+        strip_accents_ = (sa && sa->kind == JValue::Bool) ? sa->b : lowercase_;  // null follows lowercase (bert.rs)
+    }
+    const JValue *pre = root.get("pre_tokenizer");
+    has_pretok_ = pre && pre->kind == JValue::Obj;
+    if (has_pretok_) {
+        const JValue *t = pre->get("type");
+        if (!t || t->kind != JValue::Str || t->str != "BertPreTokenizer") { err = "pre_tokenizer type not supported (only BertPreTokenizer)"; return false; }
+    }
+    if (const JValue *at = root.get("added_tokens")) {
+        if (at->kind == JValue::Arr)
+            for (const JValue &a : at->arr) {
+                const JValue *c = a.get("content"), *id = a.get("id");
+                if (!c || c->kind != JValue::Str || !id || c->str.empty()) continue;
+                auto fl = [&](const char *k, bool dflt) { const JValue *v = a.get(k); return (v && v->kind == JValue::Bool) ? v->b : dflt; };
+                added_.push_back({c->str, (int32_t)id->num, fl("single_word", false), fl("lstrip", false), fl("rstrip", false), fl("normalized", false)});
+            }
+    }
+    if (const JValue *tr = root.get("truncation"))
+        if (tr->kind == JValue::Obj)
+            if (const JValue *ml = tr->get("max_length")) if (ml->kind == JValue::Num) trunc_max_ = (int)ml->num;
+    return true;
+}
+
+std::vector<uint32_t> WordPieceTokenizer::normalize(const std::vector<uint32_t> &in) const {
+    if (!has_normalizer_) return in;
+    std::vector<uint32_t> a;
+    a.reserve(in.size() + 16);
+    if (clean_text_) {
+        for (uint32_t c : in) {
+            if (c == 0 || c == 0xFFFD || is_control(c)) continue;
+            a.push_back(is_whitespace(c) ? ' ' : c);
+        }
+    } else a = in;
+    if (chinese_) {
+        std::vector<uint32_t> b;
+        b.reserve(a.size() + 16);
+        for (uint32_t c : a) {
+            if (is_chinese(c)) { b.push_back(' '); b.push_back(c); b.push_back(' '); }
+            else b.push_back(c);
+        }
+        a.swap(b);
+    }
+    if (strip_accents_) {
+        std::vector<uint32_t> d = nfd(a);
+        a.clear();
+        for (uint32_t c : d) if (!in_ranges(kMn, c)) a.push_back(c);
+    }
+    if (lowercase_) {
+        std::vector<uint32_t> b;
+        b.reserve(a.size() + 8);
+        for (uint32_t c : a) lower_append(c, b);
+        a.swap(b);
+    }
+    return a;
+}
+
+void WordPieceTokenizer::wordpiece(const std::vector<uint32_t> &word, std::vector<int32_t> &out) const {
+    const int n = (int)word.size();
+    if (n == 0) return;
+    if (n > max_chars_) { out.push_back(unk_id_); return; }
+    std::vector<int32_t> pieces;
+    int start = 0;
+    std::string cand;
+    while (start < n) {
+        int end = n;
+        int32_t found = -1;
+        while (start < end) {
+            cand = start > 0 ? prefix_ : std::string();
+            cand += encode_utf8(word.data() + start, word.data() + end);
+            auto it = vocab_.find(cand);
+            if (it != vocab_.end()) { found = it->second; break; }
+            end--;
+        }
+        if (found < 0) { out.push_back(unk_id_); return; }  // the whole word becomes [UNK]
+        pieces.push_back(found);
+        start = end;
+    }
+    out.insert(out.end(), pieces.begin(), pieces.end());
+}
+
+void WordPieceTokenizer::encode_piece(const std::string &piece, std::vector<int32_t> &out) const {
+    const std::vector<uint32_t> cps = normalize(decode_utf8(piece));
+    std::vector<uint32_t> word;
+    auto flush = [&]() { if (!word.empty()) { wordpiece(word, out); word.clear(); } };
+    for (uint32_t c : cps) {
+        if (has_pretok_) {
+            if (is_whitespace(c)) { flush(); continue; }
+            if (is_punct(c)) { flush(); word.push_back(c); flush(); continue; }
+        }
+        word.push_back(c);
+    }
+    flush();
+}
+
+std::vector<int32_t> WordPieceTokenizer::encode(const std::string &text) const {
+    std::vector<int32_t> out;
+    // added (special) tokens are cut out of the raw text first: leftmost match, longest content on ties
+    size_t pos = 0, seg = 0;
+    const size_t n = text.size();
+    auto is_word_byte = [&](size_t i) { const unsigned char c = (unsigned char)text[i]; return c >= 0x80 || (c >= '0' && c <= '9') || (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z') || c == '_'; };
+    while (pos < n && !added_.empty()) {
+        const Added *best = nullptr;
+        for (const Added &a : added_) {
+            if (a.content.size() > n - pos || text.compare(pos, a.content.size(), a.content) != 0) continue;
+            if (a.single_word) {
+                const size_t e = pos + a.content.size();
+                if ((pos > 0 && is_word_byte(pos - 1)) || (e < n && is_word_byte(e))) continue;
+            }
+            if (!best || a.content.size() > best->content.size()) best = &a;
+        }
+        if (!best) { pos++; continue; }
+        size_t left_end = pos, right_begin = pos + best->content.size();
+        if (best->lstrip) while (left_end > seg && (text[left_end - 1] == ' ' || text[left_end - 1] == '\t' || text[left_end - 1] == '\n')) left_end--;
+        if (best->rstrip) while (right_begin < n && (text[right_begin] == ' ' || text[right_begin] == '\t' || text[right_begin] == '\n')) right_begin++;
+        if (left_end > seg) encode_piece(text.substr(seg, left_end - seg), out);
+        out.push_back(best->id);
+        pos = seg = right_begin;
+    }
+    if (seg < n) encode_piece(text.substr(seg), out);
+    if (trunc_max_ >= 0 && (int)out.size() > trunc_max_) out.resize(trunc_max_);
+    return out;
+}
+
+}  // namespace bk

@@ -61,9 +61,10 @@ BK_API int bk_engine_finalize(bk_engine *e);
  * H2D copy, all kernels and the D2H copy run on the engine's stream; returns after it drained. */
 BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq, float *out);
 
-/* Same work with the inputs already resident in HBM (bench.py `value` leg): stage once, then run
- * the kernels `iters` times, timed with CUDA events on the engine's stream.
- * ms_total = elapsed ms for all iters; per-kernel-class ms via bk_engine_kernel_ms(). */
+/* Same work with the inputs already resident in HBM (bench.py `value` leg): stage a whole job once
+ * (any number of sentences, in the caller's order; it is cut into micro-batches of <= cap_tokens /
+ * cap_seqs), then run the kernels over all of it `iters` times, timed with CUDA events on the
+ * engine's stream.  ms_total = elapsed ms for all iters; per-kernel-class ms via bk_engine_kernel_ms(). */
 BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq);
 BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernels, float *ms_total);
 BK_API int bk_engine_read_output(bk_engine *e, float *out, int32_t n_seq);
@@ -74,6 +75,8 @@ BK_API int bk_engine_kernel_ms(bk_engine *e, float *ms, int32_t *launches);
 BK_API int bk_engine_read_hidden(bk_engine *e, int32_t which, float *out);
 BK_API int bk_engine_set_keep_hidden(bk_engine *e, int32_t on);
 BK_API int64_t bk_engine_launch_count(bk_engine *e); /* kernels launched since creation */
+/* cudaProfilerStart (on=1) / cudaProfilerStop (on=0): lets `ncu --profile-from-start off` see only the timed region */
+BK_API int bk_profiler_range(int32_t on);
 
 /* ---- single-kernel entry points (tests/, profiles): host buffers in, host buffers out --------
  * f16 buffers are raw IEEE binary16 bit patterns (uint16_t). */
@@ -93,6 +96,16 @@ BK_API int bk_test_attention(int device, int32_t n_seq, const int32_t *lens, int
                              const uint16_t *qkv, int32_t qmode, uint16_t *out);
 /* mean over tokens + L2 normalise; bert.cpp:995-1006 */
 BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t d, const uint16_t *x, float *out);
+
+/* ---- host-side tokenizer alone (no GPU needed; tests/test_tokenizer.py) -------------------------
+ * Replaces bert_tokenizer::load / encode (tokenizer.cpp:30-53 -> Rust tokenizers crate):
+ * json = contents of the GGUF key blob.tokenizer.json; encode() = ids without [CLS]/[SEP]
+ * (add_special_tokens = false, huggingface_tokenizer.cc:28-35).  Returns the number of ids
+ * (written up to max_ids), or -1. */
+typedef struct bk_tokenizer bk_tokenizer;
+BK_API bk_tokenizer *bk_tokenizer_create(const char *json, int64_t json_len);
+BK_API void          bk_tokenizer_destroy(bk_tokenizer *t);
+BK_API int32_t       bk_tokenizer_encode(const bk_tokenizer *t, const char *text, int32_t *ids, int32_t max_ids);
 
 #ifdef __cplusplus
 }
