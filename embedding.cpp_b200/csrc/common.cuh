@@ -76,6 +76,20 @@ __device__ __forceinline__ void bulk_load_1d(void *smem_dst, const void *gsrc, u
         ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
 }
+// 2-D tiled store shared -> global (bulk async-group completion); rows/columns outside the tensor are clipped
+__device__ __forceinline__ void tma_store_2d(const void *tmap, const void *smem_src, int32_t c0, int32_t c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(tmap), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the newest kPending bulk groups of this thread have finished READING their shared-memory source
+template <int kPending>
+__device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory"); }
+template <int kPending>
+__device__ __forceinline__ void bulk_wait_group() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(kPending) : "memory"); }
+// named barrier among `count` threads (count % 32 == 0); id 0 is __syncthreads
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 // generic-proxy writes to smem -> visible to the async proxy (UMMA / TMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -153,6 +167,22 @@ __device__ __forceinline__ float gelu_ref(float x) {
                                   __fadd_rn(1.0f, __fmul_rn(__fmul_rn(0.044715f, u), u)));
     const float g = __fmul_rn(__fmul_rn(0.5f, u), __fadd_rn(1.0f, tanhf(inner)));
     return round_f16(g);
+}
+
+// The same function for the GEMM epilogue without a tanhf call: tanh(u) = 2*sigmoid(2u) - 1 with
+// sigmoid(2u) = 1 / (1 + 2^(-2u*log2(e))), u = sqrt(2/pi) x (1 + 0.044715 x^2), from ex2.approx / rcp.approx
+// (accurate to ~2^-22).  The reference forms fl(1 + fl(tanhf(u))) in fp32, which for x < -3 cancels down to
+// a multiple of 2^-24; rounding t = fl(2r - 1) to fp32 first and then adding 1 reproduces that cancellation,
+// so the f16 result equals the table's except on a handful of near-ties (tests/test_gpu_kernels.py counts
+// them over all 63488 finite f16 inputs).
+__device__ __forceinline__ float gelu_fast(float x) {
+    const float u = round_f16(x);
+    const float z = u * fmaf(-0.1029432395800235f, u * u, -2.302208198144325f);  // -2u*log2(e)
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+    const float t = fmaf(2.0f, r, -1.0f);  // tanh(u) rounded to fp32
+    return round_f16(__fmul_rn(__fmul_rn(0.5f, u), __fadd_rn(1.0f, t)));
 }
 
 // Q8_0 / Q8_1 activation rounding of one 32-element block given its amax (quantize_row_q8_0 /

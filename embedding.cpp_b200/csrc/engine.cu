@@ -54,7 +54,7 @@ struct Layer {
     __half *wqkv = nullptr, *wo = nullptr, *w1 = nullptr, *w2 = nullptr;
     float *bqkv = nullptr;
     const float *bo = nullptr, *b1 = nullptr, *b2 = nullptr, *ln1g = nullptr, *ln1b = nullptr, *ln2g = nullptr, *ln2b = nullptr;
-    CUtensorMap tm_wqkv, tm_wo, tm_w1, tm_w2;
+    WeightMaps tm_wqkv, tm_wo, tm_w1, tm_w2;
 };
 
 static size_t tensor_bytes(int type, int64_t ne0, int64_t ne1) {
@@ -88,6 +88,8 @@ struct bk_engine {
     __half *x = nullptr, *xq = nullptr, *qkv = nullptr, *att = nullptr, *pre = nullptr, *y = nullptr, *yq = nullptr, *h = nullptr;
     float *d_out = nullptr;
     CUtensorMap tm_x, tm_att, tm_y, tm_h;  // A-operand maps (x/y point at the Q8-rounded copy for Q4 models)
+    CUtensorMap to_qkv, to_pre, to_h;      // GEMM output maps (TMA stores), box {64, 128}
+    CUtensorMap tr_x, tr_y;                // residual maps (unrounded x / y), box {64, 128}
     // pinned staging
     int32_t *h_tokens = nullptr, *h_lens = nullptr;
     float *h_out = nullptr;
@@ -271,10 +273,8 @@ BK_API int bk_engine_finalize(bk_engine *e) {
         L.ln1b = (const float *)e->tens[L_SLOT(l, S_LN1B)].dev;
         L.ln2g = (const float *)e->tens[L_SLOT(l, S_LN2G)].dev;
         L.ln2b = (const float *)e->tens[L_SLOT(l, S_LN2B)].dev;
-        bool ok = make_tmap_f16_2d(&L.tm_wqkv, L.wqkv, d, 3 * d, d * 2, GEMM_BLOCK_K, gemm_block_n(3 * (int)d)) &&
-                  make_tmap_f16_2d(&L.tm_wo, L.wo, d, d, d * 2, GEMM_BLOCK_K, gemm_block_n((int)d)) &&
-                  make_tmap_f16_2d(&L.tm_w1, L.w1, d, f, d * 2, GEMM_BLOCK_K, gemm_block_n((int)f)) &&
-                  make_tmap_f16_2d(&L.tm_w2, L.w2, f, d, f * 2, GEMM_BLOCK_K, gemm_block_n((int)d));
+        bool ok = make_weight_maps(&L.tm_wqkv, L.wqkv, 3 * (int)d, (int)d) && make_weight_maps(&L.tm_wo, L.wo, (int)d, (int)d) &&
+                  make_weight_maps(&L.tm_w1, L.w1, (int)f, (int)d) && make_weight_maps(&L.tm_w2, L.w2, (int)d, (int)f);
         if (!ok) return fail("cuTensorMapEncodeTiled failed for layer %d weights", l);
     }
     CK(cudaStreamSynchronize(e->st));
@@ -287,7 +287,12 @@ BK_API int bk_engine_finalize(bk_engine *e) {
     bool ok = make_tmap_f16_2d(&e->tm_x, e->qmode ? e->xq : e->x, d, T, d * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) &&
               make_tmap_f16_2d(&e->tm_att, e->att, d, T, d * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) &&
               make_tmap_f16_2d(&e->tm_y, e->qmode ? e->yq : e->y, d, T, d * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) &&
-              make_tmap_f16_2d(&e->tm_h, e->h, f, T, f * 2, GEMM_BLOCK_K, GEMM_BLOCK_M);
+              make_tmap_f16_2d(&e->tm_h, e->h, f, T, f * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->to_qkv, e->qkv, 3 * d, T, 3 * d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->to_pre, e->pre, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->to_h, e->h, f, T, f * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->tr_x, e->x, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
+              make_tmap_f16_2d(&e->tr_y, e->y, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M);
     if (!ok) return fail("cuTensorMapEncodeTiled failed for activation buffers");
     e->finalized = true;
     return 0;
@@ -316,12 +321,12 @@ struct KTimer {  // brackets one kernel class with two events when timing is on
     }
 };
 
-int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const CUtensorMap &tmB, int M, int N, int K, const float *bias,
-             const __half *resid, int ldr, __half *out, int ldo, int epi) {
+int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const WeightMaps &W, int M, int N, int K, const float *bias,
+             const CUtensorMap *tmRes, const CUtensorMap &tmOut, int epi) {
     KTimer t(e, kind);
     GemmParams p;
-    p.M = M; p.N = N; p.K = K; p.bias = bias; p.resid = resid; p.ldr = ldr; p.out = out; p.ldo = ldo; p.epi = epi;
-    CK(launch_gemm(tmA, tmB, p, e->num_sms, e->st));
+    p.M = M; p.N = N; p.K = K; p.bias = bias; p.epi = epi;
+    CK(launch_gemm(tmA, W, tmOut, tmRes, p, e->num_sms, e->st));
     e->launch_count++;
     return 0;
 }
@@ -349,21 +354,21 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
     if (e->keep_hidden) CK(cudaMemcpyAsync(e->hidden, e->x, (size_t)T * d * 2, cudaMemcpyDeviceToDevice, e->st));
     for (int l = 0; l < hp.n_layer; l++) {
         Layer &L = e->layers[l];
-        if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, T, 3 * d, d, L.bqkv, nullptr, 0, e->qkv, 3 * d, BK_EPI_BIAS)) return -1;
+        if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, T, 3 * d, d, L.bqkv, nullptr, e->to_qkv, BK_EPI_BIAS)) return -1;
         {
             KTimer t(e, BK_K_ATTN);
             CK(launch_attention(e->qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
             e->launch_count++;
         }
-        if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, T, d, d, L.bo, e->x, d, e->pre, d, BK_EPI_BIAS_RESID)) return -1;
+        if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, T, d, d, L.bo, &e->tr_x, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
         {
             KTimer t(e, BK_K_ADD_LN);
             CK(launch_add_ln(e->pre, L.ln1g, L.ln1b, T, d, hp.eps, e->y, e->yq, q, e->st));
             e->launch_count++;
         }
         const int epi1 = q == 0 ? BK_EPI_BIAS_GELU : q == 1 ? BK_EPI_BIAS_GELU_Q8_0 : BK_EPI_BIAS_GELU_Q8_1;
-        if (run_gemm(e, BK_K_GEMM_FF1, e->tm_y, L.tm_w1, T, f, d, L.b1, nullptr, 0, e->h, f, epi1)) return -1;
-        if (run_gemm(e, BK_K_GEMM_FF2, e->tm_h, L.tm_w2, T, d, f, L.b2, e->y, d, e->pre, d, BK_EPI_BIAS_RESID)) return -1;
+        if (run_gemm(e, BK_K_GEMM_FF1, e->tm_y, L.tm_w1, T, f, d, L.b1, nullptr, e->to_h, epi1)) return -1;
+        if (run_gemm(e, BK_K_GEMM_FF2, e->tm_h, L.tm_w2, T, d, f, L.b2, &e->tr_y, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
         {
             KTimer t(e, BK_K_ADD_LN);
             CK(launch_add_ln(e->pre, L.ln2g, L.ln2b, T, d, hp.eps, e->x, e->xq, q, e->st));

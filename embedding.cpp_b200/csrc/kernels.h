@@ -8,25 +8,32 @@
 namespace bk {
 
 // ---- gemm_tcgen05.cu ------------------------------------------------------------------------
-// out[M][N] = epi(A[M][K] . W[N][K]^T + bias)   A, W: f16, K contiguous; fp32 accumulation in TMEM.
+// out[M][N] = epi(A[M][K] . W[N][K]^T + bias (+ resid))   A, W, out, resid: f16, fp32 accumulation in TMEM.
 struct GemmParams {
     int M, N, K;
-    const float *bias;    // [N]
-    const __half *resid;  // [M][ldr] (EPI_BIAS_RESID) or nullptr
-    int ldr;
-    __half *out;          // [M][ldo]
-    int ldo;
-    int epi;              // BK_EPI_*
+    const float *bias;  // [N]
+    int epi;            // BK_EPI_*
 };
-// box rows of the two TMA descriptors the kernel expects for a given N (tile width selection)
-int gemm_block_n(int N);
 constexpr int GEMM_BLOCK_M = 128;
 constexpr int GEMM_BLOCK_K = 64;
-// tmA: 2-D map over A {K, M} box {64, 128}; tmB: map over W {K, N} box {64, gemm_block_n(N)}; both SWIZZLE_128B
-cudaError_t launch_gemm(const CUtensorMap &tmA, const CUtensorMap &tmB, const GemmParams &p, int num_sms, cudaStream_t st);
+constexpr int GEMM_OUT_BOX_N = 64;  // columns of one output / residual TMA box (128 B of f16, 128-byte swizzle)
+// TMA descriptors of one weight matrix W[N][K] (K contiguous), one per tile width BN = 64, 128, 192, 256
+struct WeightMaps {
+    CUtensorMap tm[4];
+    int N = 0, K = 0;
+};
+bool make_weight_maps(WeightMaps *w, const void *base, int N, int K);
+// tile width that minimises wave-quantisation loss for an M x N problem on num_sms persistent CTAs
+int gemm_pick_bn(int M, int N, int num_sms);
+// tmA: map over A {K, M} box {64, 128}; tmOut / tmRes: maps over out / resid {N, M} box {64, 128}; all SWIZZLE_128B.
+// tmRes may be null unless epi == BK_EPI_BIAS_RESID.  Rows >= the maps' row count are never written.
+cudaError_t launch_gemm(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap *tmRes,
+                        const GemmParams &p, int num_sms, cudaStream_t st, int force_bn = 0);
 // 2-D f16 row-major tensor map (inner = contiguous dim) with 128-byte swizzle
 bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_t rows, uint64_t row_stride_bytes,
                       uint32_t box_inner, uint32_t box_rows);
+// y[i] = the epilogue's GELU of x[i] (tests)
+cudaError_t launch_gelu_test(const float *x, float *y, int n, cudaStream_t st);
 
 // ---- rowwise.cu -----------------------------------------------------------------------------
 // cu_seqlens (exclusive prefix sum of lens, n_seq+1 entries) and per-token position inside its sentence

@@ -107,28 +107,28 @@ __device__ __forceinline__ void load_row8(const void *tab, int wtype, int64_t r,
 
 // --------------------------------------------------------------- LN core on registers (one warp)
 // v[it][8] holds chunk c = lane + 32*it of the row (valid iff c < d/8).
-template <bool kWriteQ>
-__device__ __forceinline__ void ln_store(float (&v)[kMaxChunks][8], int d, float eps, const float *__restrict__ gamma,
+template <bool kWriteQ, int NIT>
+__device__ __forceinline__ void ln_store(float (&v)[NIT][8], int d, float eps, const float *__restrict__ gamma,
                                          const float *__restrict__ beta, __half *__restrict__ y, __half *__restrict__ yq, int qmode) {
     const int lane = lane_id();
     const int nch = d >> 3;
     float s = 0.f;
 #pragma unroll
-    for (int it = 0; it < kMaxChunks; it++)
+    for (int it = 0; it < NIT; it++)
         if (lane + 32 * it < nch)
 #pragma unroll
             for (int j = 0; j < 8; j++) s += v[it][j];
     const float mean = warp_sum(s) / (float)d;
     float s2 = 0.f;
 #pragma unroll
-    for (int it = 0; it < kMaxChunks; it++)
+    for (int it = 0; it < NIT; it++)
         if (lane + 32 * it < nch)
 #pragma unroll
             for (int j = 0; j < 8; j++) { const float t = v[it][j] - mean; v[it][j] = t; s2 += t * t; }
     const float var = warp_sum(s2) / (float)d;
     const float scale = 1.0f / sqrtf(var + eps);
 #pragma unroll
-    for (int it = 0; it < kMaxChunks; it++) {
+    for (int it = 0; it < NIT; it++) {
         const int c = lane + 32 * it;
         const bool ok = c < nch;
         float o[8];
@@ -168,7 +168,7 @@ __device__ __forceinline__ void ln_store(float (&v)[kMaxChunks][8], int d, float
 }
 
 // ------------------------------------------------------------------------------- embed + LN
-template <bool kWriteQ>
+template <bool kWriteQ, int NIT>
 __global__ void __launch_bounds__(256) embed_ln_kernel(const EmbedParams p) {
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (t >= p.T) return;
@@ -177,9 +177,9 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const EmbedParams p) {
     int tok = __ldg(p.tokens + t);
     tok = min(max(tok, 0), p.n_vocab - 1);
     const int ps = __ldg(p.pos + t);
-    float v[kMaxChunks][8];
+    float v[NIT][8];
 #pragma unroll
-    for (int it = 0; it < kMaxChunks; it++) {
+    for (int it = 0; it < NIT; it++) {
         const int c = lane + 32 * it;
         if (c < nch) {
             float w[8], ty[8], po[8];
@@ -190,19 +190,29 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const EmbedParams p) {
             for (int j = 0; j < 8; j++) { const float a = ty[j] + w[j]; v[it][j] = po[j] + a; }  // (type + word) + pos, bert.cpp:880-887
         }
     }
-    ln_store<kWriteQ>(v, p.d, p.eps, p.gamma, p.beta, p.x + (size_t)t * p.d, kWriteQ ? p.xq + (size_t)t * p.d : nullptr, p.qmode);
+    ln_store<kWriteQ, NIT>(v, p.d, p.eps, p.gamma, p.beta, p.x + (size_t)t * p.d, kWriteQ ? p.xq + (size_t)t * p.d : nullptr, p.qmode);
 }
 cudaError_t launch_embed_ln(const EmbedParams &p, cudaStream_t st) {
     if (p.d % 32 != 0 || p.d > kMaxChunks * 256) return cudaErrorInvalidValue;
     const int wpb = 8;
     const int grid = (p.T + wpb - 1) / wpb;
-    if (p.qmode) embed_ln_kernel<true><<<grid, wpb * 32, 0, st>>>(p);
-    else embed_ln_kernel<false><<<grid, wpb * 32, 0, st>>>(p);
+    const int nit = (p.d + 255) / 256;  // 16-byte chunks per lane
+#define BK_EMBED(NIT)                                                        \
+    do {                                                                     \
+        if (p.qmode) embed_ln_kernel<true, NIT><<<grid, wpb * 32, 0, st>>>(p); \
+        else embed_ln_kernel<false, NIT><<<grid, wpb * 32, 0, st>>>(p);        \
+    } while (0)
+    if (nit <= 1) BK_EMBED(1);
+    else if (nit == 2) BK_EMBED(2);
+    else if (nit == 3) BK_EMBED(3);
+    else if (nit == 4) BK_EMBED(4);
+    else BK_EMBED(kMaxChunks);
+#undef BK_EMBED
     return cudaGetLastError();
 }
 
 // --------------------------------------------------------------------------------- add + LN
-template <bool kWriteQ>
+template <bool kWriteQ, int NIT>
 __global__ void __launch_bounds__(256) add_ln_kernel(const __half *__restrict__ pre, const float *__restrict__ gamma,
                                                      const float *__restrict__ beta, int T, int d, float eps,
                                                      __half *__restrict__ y, __half *__restrict__ yq, int qmode) {
@@ -211,13 +221,13 @@ __global__ void __launch_bounds__(256) add_ln_kernel(const __half *__restrict__ 
     const int lane = lane_id();
     const int nch = d >> 3;
     const uint4 *src = reinterpret_cast<const uint4 *>(pre + (size_t)t * d);
-    float v[kMaxChunks][8];
-    uint4 u[kMaxChunks];
+    float v[NIT][8];
+    uint4 u[NIT];
 #pragma unroll
-    for (int it = 0; it < kMaxChunks; it++)
+    for (int it = 0; it < NIT; it++)
         if (lane + 32 * it < nch) u[it] = __ldg(src + lane + 32 * it);
 #pragma unroll
-    for (int it = 0; it < kMaxChunks; it++)
+    for (int it = 0; it < NIT; it++)
         if (lane + 32 * it < nch) {
             float2 f;
             f = unpack_h2(u[it].x); v[it][0] = f.x; v[it][1] = f.y;
@@ -225,15 +235,25 @@ __global__ void __launch_bounds__(256) add_ln_kernel(const __half *__restrict__ 
             f = unpack_h2(u[it].z); v[it][4] = f.x; v[it][5] = f.y;
             f = unpack_h2(u[it].w); v[it][6] = f.x; v[it][7] = f.y;
         }
-    ln_store<kWriteQ>(v, d, eps, gamma, beta, y + (size_t)t * d, kWriteQ ? yq + (size_t)t * d : nullptr, qmode);
+    ln_store<kWriteQ, NIT>(v, d, eps, gamma, beta, y + (size_t)t * d, kWriteQ ? yq + (size_t)t * d : nullptr, qmode);
 }
 cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *beta, int T, int d, float eps, __half *y,
                           __half *yq, int qmode, cudaStream_t st) {
     if (d % 32 != 0 || d > kMaxChunks * 256) return cudaErrorInvalidValue;
     const int wpb = 8;
     const int grid = (T + wpb - 1) / wpb;
-    if (qmode) add_ln_kernel<true><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, qmode);
-    else add_ln_kernel<false><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, 0);
+    const int nit = (d + 255) / 256;  // 16-byte chunks per lane
+#define BK_ADDLN(NIT)                                                                                          \
+    do {                                                                                                       \
+        if (qmode) add_ln_kernel<true, NIT><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, qmode); \
+        else add_ln_kernel<false, NIT><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, 0);          \
+    } while (0)
+    if (nit <= 1) BK_ADDLN(1);
+    else if (nit == 2) BK_ADDLN(2);
+    else if (nit == 3) BK_ADDLN(3);
+    else if (nit == 4) BK_ADDLN(4);
+    else BK_ADDLN(kMaxChunks);
+#undef BK_ADDLN
     return cudaGetLastError();
 }
 

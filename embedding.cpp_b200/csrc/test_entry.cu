@@ -54,22 +54,25 @@ BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint1
     if (resid) TCK(cudaMemcpy(dR.p, resid, (size_t)M * N * 2, cudaMemcpyHostToDevice));
     TCK(cudaMemset(dO.p, 0xFF, (size_t)M * N * 2));
     TCK(launch_weight_to_f16(dWraw.p, wtype, N, K, dW.as<__half>(), 0));
-    CUtensorMap tmA, tmB;
-    if (!make_tmap_f16_2d(&tmA, dA.p, K, M, (uint64_t)K * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) ||
-        !make_tmap_f16_2d(&tmB, dW.p, K, N, (uint64_t)K * 2, GEMM_BLOCK_K, gemm_block_n(N))) {
+    CUtensorMap tmA, tmO, tmR;
+    WeightMaps wm;
+    if (!make_tmap_f16_2d(&tmA, dA.p, K, M, (uint64_t)K * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) || !make_weight_maps(&wm, dW.p, N, K) ||
+        !make_tmap_f16_2d(&tmO, dO.p, N, M, (uint64_t)N * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) ||
+        !make_tmap_f16_2d(&tmR, dR.p, N, M, (uint64_t)N * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M)) {
         fprintf(stderr, "bk_test_gemm: cuTensorMapEncodeTiled failed\n");
         return -1;
     }
     GemmParams p;
-    p.M = M; p.N = N; p.K = K; p.bias = dB.as<float>(); p.resid = resid ? dR.as<__half>() : nullptr; p.ldr = N;
-    p.out = dO.as<__half>(); p.ldo = N; p.epi = epi;
+    p.M = M; p.N = N; p.K = K; p.bias = dB.as<float>(); p.epi = epi;
+    const int bn = epi >> 8;  // tests may force a tile width: epi | (BN << 8)
+    p.epi = epi & 0xFF;
     cudaEvent_t a, b;
     TCK(cudaEventCreate(&a)); TCK(cudaEventCreate(&b));
-    TCK(launch_gemm(tmA, tmB, p, prop.multiProcessorCount, 0));  // warm-up (also first-use setup)
+    TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn));  // warm-up (also first-use setup)
     TCK(cudaDeviceSynchronize());
     const int reps = ms ? 5 : 1;
     TCK(cudaEventRecord(a, 0));
-    for (int i = 0; i < reps; i++) TCK(launch_gemm(tmA, tmB, p, prop.multiProcessorCount, 0));
+    for (int i = 0; i < reps; i++) TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn));
     TCK(cudaEventRecord(b, 0));
     TCK(cudaDeviceSynchronize());
     float t = 0;
@@ -77,6 +80,17 @@ BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint1
     if (ms) *ms = t / reps;
     cudaEventDestroy(a); cudaEventDestroy(b);
     TCK(cudaMemcpy(out, dO.p, (size_t)M * N * 2, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+BK_API int bk_test_gelu(int device, int32_t n, const float *x, float *y) {
+    TCK(cudaSetDevice(device));
+    DevBuf dX, dY;
+    TCK(dX.alloc((size_t)n * 4)); TCK(dY.alloc((size_t)n * 4));
+    TCK(cudaMemcpy(dX.p, x, (size_t)n * 4, cudaMemcpyHostToDevice));
+    TCK(launch_gelu_test(dX.as<float>(), dY.as<float>(), n, 0));
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(y, dY.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -83,10 +83,13 @@ BK_API int bk_profiler_range(int32_t on);
 enum { BK_EPI_BIAS = 0, BK_EPI_BIAS_RESID = 1, BK_EPI_BIAS_GELU = 2, BK_EPI_BIAS_GELU_Q8_0 = 3, BK_EPI_BIAS_GELU_Q8_1 = 4 };
 /* out[M][N] = epi(A[M][K] . W[N][K]^T + bias[N] (+ resid[M][N]))   -- ggml_mul_mat + bias add,
  * ggml.c:9388-9597, bert.cpp:909-910.  wtype selects how W is stored (BK_F16 raw halves,
- * BK_Q4_0/BK_Q4_1 GGUF blocks along K, BK_F32 floats). */
+ * BK_Q4_0/BK_Q4_1 GGUF blocks along K, BK_F32 floats).  epi may carry a forced tile width in bits 8..:
+ * epi | (BN << 8), BN in {64,128,192,256} (0 = automatic choice). */
 BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint16_t *A, const void *W,
                         int32_t wtype, const float *bias, const uint16_t *resid, int32_t epi,
                         uint16_t *out, float *ms);
+/* the GEMM epilogue's GELU alone: y[i] = f16(gelu(f16(x[i]))) -- ggml_vec_gelu_f32's f16 table, ggml.c:1418-1441 */
+BK_API int bk_test_gelu(int device, int32_t n, const float *x, float *y);
 /* LN(x)*gamma+beta over rows of `pre` (f16) -> y f16 (+ yq = Q8-rounded copy when qmode 1=Q8_0, 2=Q8_1);
  * ggml_norm + mul + add, ggml.c:8976-9004, bert.cpp:958-963 */
 BK_API int bk_test_add_ln(int device, int32_t T, int32_t d, float eps, const uint16_t *pre, const float *gamma,

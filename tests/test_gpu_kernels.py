@@ -63,6 +63,39 @@ def test_gemm_f16_weights(lib, binding, orc, make_model, M, N, K, epi):
         assert (err <= tol).all(), (float(err.max()), np.unravel_index(err.argmax(), err.shape))
 
 
+@pytest.mark.parametrize("bn", [64, 128, 192, 256])
+@pytest.mark.parametrize("epi", [0, 1])
+def test_gemm_forced_tile_width(lib, binding, bn, epi):
+    """every tile width of the persistent kernel (the engine picks one per problem), several tiles per CTA"""
+    M, N, K = 128 * 150 + 37, 768, 256      # > 148 tiles for every width: exercises staging-box reuse across tiles
+    rng = np.random.default_rng(bn + epi)
+    A = h(rng.standard_normal((M, K)) * 0.5)
+    W = h(rng.standard_normal((N, K)) * 0.05)
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float32)
+    resid = h(rng.standard_normal((M, N))) if epi == 1 else None
+    out, _ = run_gemm(lib, A, W, binding.BK_F16, N, bias, resid, epi | (bn << 8))
+    ref = A.astype(np.float32) @ W.astype(np.float32).T + bias
+    if epi == 1:
+        ref = ref + resid.astype(np.float32)
+    err = np.abs(out.astype(np.float32) - ref)
+    assert (err <= 2e-3 * np.abs(ref) + 2e-3).all(), (float(err.max()), np.unravel_index(err.argmax(), err.shape))
+
+
+def test_gelu_all_f16_inputs(lib, orc, make_model):
+    """the epilogue's exp2/rcp GELU against the reference's f16 table (ggml.c:1433-1441) on every finite f16"""
+    x = np.arange(65536, dtype=np.uint32).astype(np.uint16).view(np.float16)
+    x = np.ascontiguousarray(x[np.isfinite(x)].astype(np.float32))
+    y = np.zeros_like(x)
+    assert lib.bk_test_gelu(0, x.size, x.ctypes.data_as(_f32p), y.ctypes.data_as(_f32p)) == 0
+    o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+    want = gelu16(o.lib, x)
+    bad = y != want
+    # differences are 1-ulp f16 near-ties only, and rare
+    assert bad.sum() <= 32, int(bad.sum())
+    ulp = np.abs(y[bad].astype(np.float16).view(np.int16).astype(np.int32) - want[bad].astype(np.float16).view(np.int16).astype(np.int32))
+    assert (ulp <= 1).all()
+
+
 @pytest.mark.parametrize("wname,wtype", [("q4_0", 2), ("q4_1", 3), ("f32", 0)])
 def test_gemm_other_weight_storage(lib, gio, wname, wtype):
     """Q4_0/Q4_1/F32 weight storage: the product decodes GGUF blocks itself; compare with the NumPy decode."""
