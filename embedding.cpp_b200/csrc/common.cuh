@@ -58,6 +58,28 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {}
 }
 
+// ---------------------------------------------------------------- CTA pair (cluster of 2) helpers
+// In a 2-CTA cluster the shared::cluster address of a CTA's own shared memory differs from its peer's only in
+// bit 24 (CUTLASS: Sm100MmaPeerBitMask); clearing it addresses the same offset in the even ("leader") CTA.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive (+ expect_tx) on a barrier given by its shared::cluster address (own or peer CTA).  Default .release.cta
+// semantics as in CUTLASS' ClusterBarrier: an explicit .release.cluster compiles to MEMBAR.ALL + ERRBAR, which
+// drains the issuing thread's outstanding TMA loads and serialises the operand ring (measured: 2x slower).
+__device__ __forceinline__ void mbar_arrive_expect_tx_cluster(uint32_t bar_addr, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------ TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void *tmap) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
@@ -67,6 +89,14 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const void *tmap, ui
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+// the same load issued by either CTA of a pair: data lands in the issuing CTA's smem, complete_tx goes to the
+// barrier at shared::cluster address bar_addr (normally the leader CTA's)
+__device__ __forceinline__ void tma_load_2d_pair(void *smem_dst, const void *tmap, uint32_t bar_addr, int32_t c0, int32_t c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(bar_addr), "r"(c0), "r"(c1)
         : "memory");
 }
 // 1-D bulk copy global -> shared (bytes multiple of 16, both 16 B aligned)
@@ -97,15 +127,21 @@ __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.p
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-// whole warp; writes the TMEM base address into *smem_dst
-template <uint32_t kCols>
+// whole warp; writes the TMEM base address into *smem_dst.  kCG = 2: the same warp of BOTH CTAs of the pair calls it.
+template <uint32_t kCols, int kCG = 1>
 __device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "n"(kCols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (kCG == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "n"(kCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "n"(kCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
 }
-template <uint32_t kCols>
+template <uint32_t kCols, int kCG = 1>
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+    if (kCG == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
 }
 
 // Shared-memory matrix descriptor for a K-major operand tile stored as rows of 128 B (64 halves)
@@ -135,6 +171,21 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// CTA-pair MMA (issued by the leader CTA only): D is 256 x N, rows 0-127 in the leader's TMEM and 128-255 in the
+// peer's; each CTA's smem holds its own 128 rows of A and its own N/2 rows of B at the descriptor addresses
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// pair commit: arrives on the barrier at this smem offset in BOTH CTAs when the MMAs issued so far complete
+__device__ __forceinline__ void umma_commit_pair(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
 // all previously issued MMAs of this thread -> arrive on an mbarrier when they complete
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -153,6 +204,50 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ------------------------------------------------------- warp-collective ("elected") issue variants
+// Called by ALL lanes of a warp in uniform control flow; the instruction is issued once, by the lane
+// elect.sync picks.  Unlike `if (lane == 0) op();` this keeps the enclosing loop warp-uniform, so ptxas keeps
+// descriptors / addresses / loop counters in uniform registers and emits back-to-back UTCHMMA / UTMALDG
+// instead of a per-instruction ELECT + R2UR "waterfall" loop (measured: ~700 -> ~250 cycles per K block).
+#define BK_ELECT_PROLOGUE "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+__device__ __forceinline__ void mbar_expect_tx_e(uint64_t *bar, uint32_t bytes) {
+    asm volatile(BK_ELECT_PROLOGUE "@e mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx_cluster_e(uint32_t bar_addr, uint32_t bytes) {
+    asm volatile(BK_ELECT_PROLOGUE "@e mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;\n\t}" ::"r"(bar_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_e(void *smem_dst, const void *tmap, uint64_t *bar, int32_t c0, int32_t c1) {
+    asm volatile(BK_ELECT_PROLOGUE
+                 "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}"
+                 ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair_e(void *smem_dst, const void *tmap, uint32_t bar_addr, int32_t c0, int32_t c1) {
+    asm volatile(BK_ELECT_PROLOGUE
+                 "@e cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}"
+                 ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(bar_addr), "r"(c0), "r"(c1)
+                 : "memory");
+}
+template <int kCG>
+__device__ __forceinline__ void umma_f16_e(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    if (kCG == 1)
+        asm volatile(BK_ELECT_PROLOGUE ".reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else
+        asm volatile(BK_ELECT_PROLOGUE ".reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "@e tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+template <int kCG>
+__device__ __forceinline__ void umma_commit_e(uint64_t *bar) {
+    if (kCG == 1)
+        asm volatile(BK_ELECT_PROLOGUE "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+    else
+        asm volatile(BK_ELECT_PROLOGUE "@e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+                     ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
 
 // ------------------------------------------------------------------------------ numerics helpers
 // round to IEEE half (RNE) and widen back: what F16C _cvtss_sh/_cvtsh_ss do (ggml-impl.h:85-101)

@@ -168,7 +168,7 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     if (hp->n_embd > 2048) { fail("unsupported n_embd %d (> 2048)", hp->n_embd); return nullptr; }
     if (hp->wtype < BK_F32 || hp->wtype > BK_Q4_1) { fail("unsupported weight type %d", hp->wtype); return nullptr; }
     if (cap_tokens < hp->n_max_tokens) cap_tokens = hp->n_max_tokens;
-    cap_tokens = (cap_tokens + 127) & ~127;
+    cap_tokens = (cap_tokens + 255) & ~255;  // whole CTA-pair tiles (256 rows): stores past T stay inside the buffers
     if (cap_seqs < 1) cap_seqs = 1;
     if (cudaSetDevice(device) != cudaSuccess) { fail("cudaSetDevice(%d) failed", device); return nullptr; }
     cudaDeviceProp prop;

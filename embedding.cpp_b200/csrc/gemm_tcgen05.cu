@@ -40,10 +40,14 @@ constexpr int kTeamThreads = 256;
 constexpr int kSmemLimit = 227 * 1024;
 constexpr int kBoxBytes = GEMM_BLOCK_M * GEMM_OUT_BOX_N * 2;  // 16 KB
 
-template <int BN>
+// CG = 1: one CTA per tile (tcgen05.mma.cta_group::1, M = 128).  CG = 2: a CTA pair (cluster of 2) per 256 x BN
+// tile: each CTA holds its own 128 rows of A and BN/2 rows of W, the leader issues cta_group::2 MMAs that read
+// both CTAs' shared memory, so every CTA streams (128 + BN/2) instead of (128 + BN) operand rows per K block.
+template <int BN, int CG>
 struct GemmCfg {
     static constexpr int A_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;  // 16 KB
-    static constexpr int B_BYTES = BN * GEMM_BLOCK_K * 2;
+    static constexpr int B_ROWS = BN / CG;                           // W rows this CTA loads per K block
+    static constexpr int B_BYTES = B_ROWS * GEMM_BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int NBOX = BN / GEMM_OUT_BOX_N;
     static constexpr int OUT_BYTES = NBOX * kBoxBytes;
@@ -57,13 +61,14 @@ struct GemmCfg {
     static_assert((2 * STAGES + 4 + 2 * NBOX) * 8 + 8 <= BAR_BYTES, "barrier area");
 };
 
-template <int BN>
+template <int BN, int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GemmParams p) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, CG>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int NBOX = Cfg::NBOX;
+    constexpr int TILE_M = GEMM_BLOCK_M * CG;  // rows of one (pair) tile
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t *ring = smem;
@@ -80,83 +85,93 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int lane = threadIdx.x & 31;
     const bool has_resid = p.epi == BK_EPI_BIAS_RESID;
 
-    const int m_tiles = (p.M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M;
+    const int m_tiles = (p.M + TILE_M - 1) / TILE_M;
     const int n_tiles = (p.N + BN - 1) / BN;
     const int num_tiles = m_tiles * n_tiles;
     const int num_kb = (p.K + GEMM_BLOCK_K - 1) / GEMM_BLOCK_K;
+    // tile walk: unit u of U (a CTA, or a CTA pair) takes tiles u, u+U, ...; rank = this CTA's half of the pair tile
+    const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
+    const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int units = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         tma_prefetch_desc(&tmOut);
         if (has_resid) tma_prefetch_desc(&tmRes);
-        for (int i = 0; i < STAGES; i++) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-        for (int i = 0; i < 2; i++) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], kEpiThreads / 32); }
+        for (int i = 0; i < STAGES; i++) { mbar_init(&full_bar[i], CG); mbar_init(&empty_bar[i], 1); }   // full: one producer arrival per CTA
+        for (int i = 0; i < 2; i++) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], CG * kEpiThreads / 32); }
         for (int i = 0; i < NBOX; i++) { mbar_init(&rfull_bar[i], 1); mbar_init(&sfree_bar[i], 1); }
         mbar_fence_init();
     }
-    if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+    if (warp == 1) tmem_alloc<Cfg::TMEM_COLS, CG>(tmem_slot);
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all();  // the peer's barriers are initialised before anything signals them
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Warps 0-2 run their loops with all 32 lanes in uniform control flow and issue through the *_e
+    // ("elected lane") wrappers -- see common.cuh for why.
     if (warp == 0) {
         // ===================================================================== TMA producer (A, W)
-        if (lane == 0) {
-            int s = 0; uint32_t ph = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t / n_tiles) * GEMM_BLOCK_M, n0 = (t % n_tiles) * BN;
-                for (int kb = 0; kb < num_kb; kb++) {
-                    mbar_wait(&empty_bar[s], ph ^ 1);
-                    uint8_t *sa = ring + s * Cfg::STAGE_BYTES, *sb = sa + Cfg::A_BYTES;
-                    mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
-                    tma_load_2d(sa, &tmA, &full_bar[s], kb * GEMM_BLOCK_K, m0);
-                    tma_load_2d(sb, &tmB, &full_bar[s], kb * GEMM_BLOCK_K, n0);
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
+        int s = 0; uint32_t ph = 0;
+        for (int t = unit; t < num_tiles; t += units) {
+            const int m0 = (t / n_tiles) * TILE_M + rank * GEMM_BLOCK_M, n0 = (t % n_tiles) * BN + rank * Cfg::B_ROWS;
+            for (int kb = 0; kb < num_kb; kb++) {
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                uint8_t *sa = ring + s * Cfg::STAGE_BYTES, *sb = sa + Cfg::A_BYTES;
+                if (CG == 1) {
+                    mbar_expect_tx_e(&full_bar[s], Cfg::STAGE_BYTES);
+                    tma_load_2d_e(sa, &tmA, &full_bar[s], kb * GEMM_BLOCK_K, m0);
+                    tma_load_2d_e(sb, &tmB, &full_bar[s], kb * GEMM_BLOCK_K, n0);
+                } else {
+                    // both CTAs report to the leader's barrier: one arrival + this CTA's bytes each
+                    const uint32_t lead_full = smem_u32(&full_bar[s]) & kPeerBitMask;
+                    mbar_arrive_expect_tx_cluster_e(lead_full, Cfg::STAGE_BYTES);
+                    tma_load_2d_pair_e(sa, &tmA, lead_full, kb * GEMM_BLOCK_K, m0);
+                    tma_load_2d_pair_e(sb, &tmB, lead_full, kb * GEMM_BLOCK_K, n0);
                 }
+                if (++s == STAGES) { s = 0; ph ^= 1; }
             }
         }
-    } else if (warp == 1) {
-        // ======================================================================= MMA issuer
-        constexpr uint32_t idesc = umma_idesc_f16(GEMM_BLOCK_M, BN);
+    } else if (warp == 1 && rank == 0) {
+        // ======================================================================= MMA issuer (leader CTA)
+        constexpr uint32_t idesc = umma_idesc_f16(TILE_M, BN);
         int s = 0; uint32_t ph = 0;
         int as = 0; uint32_t aph = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        for (int t = unit; t < num_tiles; t += units) {
             mbar_wait(&tempty_bar[as], aph ^ 1);  // epilogue has drained this accumulator stage
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
             for (int kb = 0; kb < num_kb; kb++) {
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
-                if (lane == 0) {
-                    const uint32_t sa = smem_u32(ring + s * Cfg::STAGE_BYTES);
-                    const uint64_t adesc = umma_desc_sw128(sa);
-                    const uint64_t bdesc = umma_desc_sw128(sa + Cfg::A_BYTES);
+                const uint32_t sa = smem_u32(ring + s * Cfg::STAGE_BYTES);
+                const uint64_t adesc = umma_desc_sw128(sa);
+                const uint64_t bdesc = umma_desc_sw128(sa + Cfg::A_BYTES);
 #pragma unroll
-                    for (int k = 0; k < GEMM_BLOCK_K / 16; k++) {
-                        // +32 bytes per UMMA_K step inside the swizzle atom: +2 in the (addr >> 4) field
-                        umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
-                    }
-                    umma_commit(&empty_bar[s]);                        // smem stage reusable when these MMAs retire
-                    if (kb == num_kb - 1) umma_commit(&tfull_bar[as]);  // accumulator complete
+                for (int k = 0; k < GEMM_BLOCK_K / 16; k++) {
+                    // +32 bytes per UMMA_K step inside the swizzle atom: +2 in the (addr >> 4) field
+                    umma_f16_e<CG>(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
                 }
-                __syncwarp();
+                umma_commit_e<CG>(&empty_bar[s]);                        // smem stage reusable when these MMAs retire (both CTAs of a pair)
+                if (kb == num_kb - 1) umma_commit_e<CG>(&tfull_bar[as]);  // accumulator complete
                 if (++s == STAGES) { s = 0; ph ^= 1; }
             }
             if (++as == 2) { as = 0; aph ^= 1; }
         }
     } else if (warp == 2) {
         // ================================================================= residual loader (TMA)
-        if (has_resid && lane == 0) {
+        if (has_resid) {
             uint32_t bph = 0;  // bit b = parity of the next use of box b
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t / n_tiles) * GEMM_BLOCK_M, n0 = (t % n_tiles) * BN;
+            for (int t = unit; t < num_tiles; t += units) {
+                const int m0 = (t / n_tiles) * TILE_M + rank * GEMM_BLOCK_M, n0 = (t % n_tiles) * BN;
                 for (int b = 0; b < NBOX; b++) {
                     if (n0 + b * GEMM_OUT_BOX_N >= p.N) break;
                     mbar_wait(&sfree_bar[b], ((bph >> b) & 1) ^ 1);  // the previous store of this box has read it
-                    mbar_expect_tx(&rfull_bar[b], kBoxBytes);
-                    tma_load_2d(obuf + b * kBoxBytes, &tmRes, &rfull_bar[b], n0 + b * GEMM_OUT_BOX_N, m0);
+                    mbar_expect_tx_e(&rfull_bar[b], kBoxBytes);
+                    tma_load_2d_e(obuf + b * kBoxBytes, &tmRes, &rfull_bar[b], n0 + b * GEMM_OUT_BOX_N, m0);
                     bph ^= 1u << b;
                 }
             }
@@ -175,14 +190,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         int as = 0; uint32_t aph = 0;
         uint32_t bph = 0;
         int prev_box = -1;  // issuer: box of the newest committed store group
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            const int m0 = (t / n_tiles) * GEMM_BLOCK_M, n0 = (t % n_tiles) * BN;
+        // accumulator hand-back goes to the MMA warp of the leader CTA (own CTA when CG == 1)
+        const uint32_t tempty_addr0 = smem_u32(&tempty_bar[0]) & (CG == 2 ? kPeerBitMask : 0xFFFFFFFFu);
+        for (int t = unit; t < num_tiles; t += units) {
+            const int m0 = (t / n_tiles) * TILE_M + rank * GEMM_BLOCK_M, n0 = (t % n_tiles) * BN;
             mbar_wait(&tfull_bar[as], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
             if (team >= NBOX) {  // nothing to read for this team (BN = 64)
                 tc_fence_before();
-                if (lane == 0) mbar_arrive(&tempty_bar[as]);
+                if (lane == 0) mbar_arrive_cluster(tempty_addr0 + 8u * as);
             }
 #pragma unroll 1
             for (int b = team; b < NBOX; b += 2) {
@@ -194,7 +211,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 if (b + 2 >= NBOX) {  // last read of this stage by this warp: hand the accumulator back to the MMA warp
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&tempty_bar[as]);
+                    if (lane == 0) mbar_arrive_cluster(tempty_addr0 + 8u * as);
                 }
                 if (!box_live) continue;  // uniform over the CTA
                 uint8_t *box = obuf + b * kBoxBytes;
@@ -268,62 +285,92 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all();  // the peer may still be read by the leader's MMAs / signalled until here
+    else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+        tmem_dealloc<Cfg::TMEM_COLS, CG>(tmem_base);
     }
 }
 
-// ------------------------------------------------------------------------------ tile width
+// ------------------------------------------------------------------------------ tile shape
 static const int kBnChoices[4] = {64, 128, 192, 256};
-
-int gemm_pick_bn(int M, int N, int num_sms) {
-    // cost ~ waves x BN (a tile's main loop and epilogue are both proportional to BN), divided by a
-    // per-width efficiency (wider tiles re-read less of A per FLOP and amortise per-tile overheads)
-    static const double eff[4] = {0.70, 0.90, 0.97, 1.00};
-    const long m_tiles = (M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M;
-    int best = 64;
-    double best_cost = 1e300;
-    for (int i = 0; i < 4; i++) {
-        const int bn = kBnChoices[i];
-        if (bn != 64 && N % bn != 0) continue;
-        const long tiles = m_tiles * ((N + bn - 1) / bn);
-        const long waves = (tiles + num_sms - 1) / num_sms;
-        const double cost = (double)waves * bn / eff[i];
-        if (cost < best_cost - 1e-9) { best_cost = cost; best = bn; }
-    }
-    return best;
+static const int kBRows[6] = {32, 64, 96, 128, 192, 256};  // WeightMaps::tm index <-> W rows per TMA box
+static int brow_index(int rows) {
+    for (int i = 0; i < 6; i++) if (kBRows[i] == rows) return i;
+    return -1;
 }
 
-template <int BN>
-static cudaError_t launch_bn(const CUtensorMap &tmA, const CUtensorMap &tmB, const CUtensorMap &tmOut, const CUtensorMap &tmRes,
-                             const GemmParams &p, int num_sms, cudaStream_t st) {
-    using Cfg = GemmCfg<BN>;
-    cudaError_t err = cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+void gemm_pick_tile(int M, int N, int num_sms, int *bn_out, int *cg_out) {
+    // cost ~ waves x BN (a tile's main loop and epilogue are both proportional to BN), divided by an
+    // efficiency: wider tiles and CTA pairs stream fewer operand bytes per FLOP through L2 -> smem
+    static const double eff[4] = {0.70, 0.90, 0.97, 1.00};
+    int best_bn = 64, best_cg = 1;
+    double best_cost = 1e300;
+    for (int cg = 1; cg <= 2; cg++) {
+        const long units = num_sms / cg;
+        const long m_tiles = (M + GEMM_BLOCK_M * cg - 1) / (GEMM_BLOCK_M * cg);
+        for (int i = 0; i < 4; i++) {
+            const int bn = kBnChoices[i];
+            if (bn != 64 && N % bn != 0) continue;
+            const long tiles = m_tiles * ((N + bn - 1) / bn);
+            if (cg == 2 && tiles < 2 * units) continue;  // small problems: spread over all SMs instead of pairing them
+            const long waves = (tiles + units - 1) / units;
+            const double cost = (double)waves * bn / (eff[i] * (cg == 2 ? 1.12 : 1.0));
+            if (cost < best_cost - 1e-9) { best_cost = cost; best_bn = bn; best_cg = cg; }
+        }
+    }
+    *bn_out = best_bn; *cg_out = best_cg;
+}
+
+template <int BN, int CG>
+static cudaError_t launch_cfg(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap &tmRes,
+                              const GemmParams &p, int num_sms, cudaStream_t st) {
+    using Cfg = GemmCfg<BN, CG>;
+    cudaError_t err = cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (err != cudaSuccess) return err;
-    const int m_tiles = (p.M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M, n_tiles = (p.N + BN - 1) / BN;
-    int grid = m_tiles * n_tiles;
-    if (grid > num_sms) grid = num_sms;
+    const int bi = brow_index(Cfg::B_ROWS);
+    if (bi < 0) return cudaErrorInvalidValue;
+    const int m_tiles = (p.M + GEMM_BLOCK_M * CG - 1) / (GEMM_BLOCK_M * CG), n_tiles = (p.N + BN - 1) / BN;
+    int grid = m_tiles * n_tiles * CG;
+    const int max_grid = num_sms / CG * CG;
+    if (grid > max_grid) grid = max_grid;
     if (grid < 1) return cudaSuccess;
-    gemm_tcgen05_kernel<BN><<<grid, kGemmThreads, Cfg::SMEM_BYTES, st>>>(tmA, tmB, tmOut, tmRes, p);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, CG>, tmA, W.tm[bi], tmOut, tmRes, p);
 }
 
 cudaError_t launch_gemm(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap *tmRes,
-                        const GemmParams &p, int num_sms, cudaStream_t st, int force_bn) {
+                        const GemmParams &p, int num_sms, cudaStream_t st, int force_bn, int force_cg) {
     if (p.N % 32 != 0 || p.K % 8 != 0 || W.N != p.N || W.K != p.K) return cudaErrorInvalidValue;
     if (p.epi == BK_EPI_BIAS_RESID && !tmRes) return cudaErrorInvalidValue;
     static const int env_bn = [] { const char *v = getenv("BERT_B200_GEMM_BN"); return v ? atoi(v) : 0; }();
-    int bn = force_bn ? force_bn : env_bn;
-    if (!(bn == 64 || ((bn == 128 || bn == 192 || bn == 256) && p.N % bn == 0))) bn = gemm_pick_bn(p.M, p.N, num_sms);
+    static const int env_cg = [] { const char *v = getenv("BERT_B200_GEMM_CG"); return v ? atoi(v) : 0; }();
+    int bn, cg;
+    gemm_pick_tile(p.M, p.N, num_sms, &bn, &cg);
+    const int want_bn = force_bn ? force_bn : env_bn, want_cg = force_cg ? force_cg : env_cg;
+    if (want_cg == 1 || want_cg == 2) cg = want_cg;
+    if (want_bn == 64 || ((want_bn == 128 || want_bn == 192 || want_bn == 256) && p.N % want_bn == 0)) bn = want_bn;
     const CUtensorMap &tmR = tmRes ? *tmRes : tmOut;
+#define BK_GEMM_CASE(BN_)                                                                                   \
+    case BN_:                                                                                               \
+        return cg == 2 ? launch_cfg<BN_, 2>(tmA, W, tmOut, tmR, p, num_sms, st) : launch_cfg<BN_, 1>(tmA, W, tmOut, tmR, p, num_sms, st)
     switch (bn) {
-        case 256: return launch_bn<256>(tmA, W.tm[3], tmOut, tmR, p, num_sms, st);
-        case 192: return launch_bn<192>(tmA, W.tm[2], tmOut, tmR, p, num_sms, st);
-        case 128: return launch_bn<128>(tmA, W.tm[1], tmOut, tmR, p, num_sms, st);
-        default: return launch_bn<64>(tmA, W.tm[0], tmOut, tmR, p, num_sms, st);
+        BK_GEMM_CASE(256);
+        BK_GEMM_CASE(192);
+        BK_GEMM_CASE(128);
+        default: return cg == 2 ? launch_cfg<64, 2>(tmA, W, tmOut, tmR, p, num_sms, st) : launch_cfg<64, 1>(tmA, W, tmOut, tmR, p, num_sms, st);
     }
+#undef BK_GEMM_CASE
 }
 
 // ------------------------------------------------------------------------------ tensor maps
@@ -359,8 +406,8 @@ bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_
 
 bool make_weight_maps(WeightMaps *w, const void *base, int N, int K) {
     w->N = N; w->K = K;
-    for (int i = 0; i < 4; i++)
-        if (!make_tmap_f16_2d(&w->tm[i], base, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, GEMM_BLOCK_K, (uint32_t)kBnChoices[i])) return false;
+    for (int i = 0; i < 6; i++)
+        if (!make_tmap_f16_2d(&w->tm[i], base, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, GEMM_BLOCK_K, (uint32_t)kBRows[i])) return false;
     return true;
 }
 

@@ -17,18 +17,20 @@ struct GemmParams {
 constexpr int GEMM_BLOCK_M = 128;
 constexpr int GEMM_BLOCK_K = 64;
 constexpr int GEMM_OUT_BOX_N = 64;  // columns of one output / residual TMA box (128 B of f16, 128-byte swizzle)
-// TMA descriptors of one weight matrix W[N][K] (K contiguous), one per tile width BN = 64, 128, 192, 256
+// TMA descriptors of one weight matrix W[N][K] (K contiguous), one per box height 32/64/96/128/192/256 rows
+// (= tile width BN for one-CTA tiles, BN/2 for CTA-pair tiles)
 struct WeightMaps {
-    CUtensorMap tm[4];
+    CUtensorMap tm[6];
     int N = 0, K = 0;
 };
 bool make_weight_maps(WeightMaps *w, const void *base, int N, int K);
-// tile width that minimises wave-quantisation loss for an M x N problem on num_sms persistent CTAs
-int gemm_pick_bn(int M, int N, int num_sms);
+// tile width BN and CTAs per tile (1, or 2 = CTA pair on a 256 x BN tile) that minimise wave-quantisation loss
+// for an M x N problem on num_sms persistent CTAs
+void gemm_pick_tile(int M, int N, int num_sms, int *bn, int *cg);
 // tmA: map over A {K, M} box {64, 128}; tmOut / tmRes: maps over out / resid {N, M} box {64, 128}; all SWIZZLE_128B.
 // tmRes may be null unless epi == BK_EPI_BIAS_RESID.  Rows >= the maps' row count are never written.
 cudaError_t launch_gemm(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap *tmRes,
-                        const GemmParams &p, int num_sms, cudaStream_t st, int force_bn = 0);
+                        const GemmParams &p, int num_sms, cudaStream_t st, int force_bn = 0, int force_cg = 0);
 // 2-D f16 row-major tensor map (inner = contiguous dim) with 128-byte swizzle
 bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_t rows, uint64_t row_stride_bytes,
                       uint32_t box_inner, uint32_t box_rows);

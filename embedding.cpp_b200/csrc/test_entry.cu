@@ -64,15 +64,15 @@ BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint1
     }
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.bias = dB.as<float>(); p.epi = epi;
-    const int bn = epi >> 8;  // tests may force a tile width: epi | (BN << 8)
+    const int bn = (epi >> 8) & 0xFFF, cg = epi >> 20;  // tests may force the tile: epi | (BN << 8) | (CG << 20)
     p.epi = epi & 0xFF;
     cudaEvent_t a, b;
     TCK(cudaEventCreate(&a)); TCK(cudaEventCreate(&b));
-    TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn));  // warm-up (also first-use setup)
+    TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn, cg));  // warm-up (also first-use setup)
     TCK(cudaDeviceSynchronize());
     const int reps = ms ? 5 : 1;
     TCK(cudaEventRecord(a, 0));
-    for (int i = 0; i < reps; i++) TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn));
+    for (int i = 0; i < reps; i++) TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn, cg));
     TCK(cudaEventRecord(b, 0));
     TCK(cudaDeviceSynchronize());
     float t = 0;

@@ -63,17 +63,19 @@ def test_gemm_f16_weights(lib, binding, orc, make_model, M, N, K, epi):
         assert (err <= tol).all(), (float(err.max()), np.unravel_index(err.argmax(), err.shape))
 
 
+@pytest.mark.parametrize("cg", [1, 2])
 @pytest.mark.parametrize("bn", [64, 128, 192, 256])
 @pytest.mark.parametrize("epi", [0, 1])
-def test_gemm_forced_tile_width(lib, binding, bn, epi):
-    """every tile width of the persistent kernel (the engine picks one per problem), several tiles per CTA"""
+def test_gemm_forced_tile_width(lib, binding, bn, epi, cg):
+    """every tile shape of the persistent kernel (the engine picks one per problem): width 64..256, one CTA
+    per 128-row tile or a CTA pair (cta_group::2) per 256-row tile; several tiles per CTA"""
     M, N, K = 128 * 150 + 37, 768, 256      # > 148 tiles for every width: exercises staging-box reuse across tiles
-    rng = np.random.default_rng(bn + epi)
+    rng = np.random.default_rng(bn + epi + cg)
     A = h(rng.standard_normal((M, K)) * 0.5)
     W = h(rng.standard_normal((N, K)) * 0.05)
     bias = (rng.standard_normal(N) * 0.1).astype(np.float32)
     resid = h(rng.standard_normal((M, N))) if epi == 1 else None
-    out, _ = run_gemm(lib, A, W, binding.BK_F16, N, bias, resid, epi | (bn << 8))
+    out, _ = run_gemm(lib, A, W, binding.BK_F16, N, bias, resid, epi | (bn << 8) | (cg << 20))
     ref = A.astype(np.float32) @ W.astype(np.float32).T + bias
     if epi == 1:
         ref = ref + resid.astype(np.float32)
