@@ -90,6 +90,7 @@ struct bk_engine {
     CUtensorMap tm_x, tm_att, tm_y, tm_h;  // A-operand maps (x/y point at the Q8-rounded copy for Q4 models)
     CUtensorMap to_qkv, to_pre, to_h;      // GEMM output maps (TMA stores), box {64, 128}
     CUtensorMap tr_x, tr_y;                // residual maps (unrounded x / y), box {64, 128}
+    CUtensorMap ta_qkv;                    // attention's view of qkv: box {dh, 64 rows}
     // pinned staging
     int32_t *h_tokens = nullptr, *h_lens = nullptr;
     float *h_out = nullptr;
@@ -148,6 +149,7 @@ static int engine_alloc(bk_engine *e) {
     CK(cudaMallocHost(&e->h_out, (size_t)e->cap_seqs * d * 4));
     // the GEMM A operand may read (never store) rows past T inside the last 128-row tile: keep them finite
     CK(cudaMemsetAsync(e->x, 0, T * d * 2, e->st));
+    CK(cudaMemsetAsync(e->qkv, 0, T * 3 * d * 2, e->st));  // attention's MMAs read up to 15 K/V rows past a sentence: finite
     CK(cudaMemsetAsync(e->att, 0, T * d * 2, e->st));
     CK(cudaMemsetAsync(e->y, 0, T * d * 2, e->st));
     CK(cudaMemsetAsync(e->h, 0, T * f * 2, e->st));
@@ -292,7 +294,8 @@ BK_API int bk_engine_finalize(bk_engine *e) {
               make_tmap_f16_2d(&e->to_pre, e->pre, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
               make_tmap_f16_2d(&e->to_h, e->h, f, T, f * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
               make_tmap_f16_2d(&e->tr_x, e->x, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
-              make_tmap_f16_2d(&e->tr_y, e->y, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M);
+              make_tmap_f16_2d(&e->tr_y, e->y, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
+              make_tmap_attention(&e->ta_qkv, e->qkv, (int)d, hp.n_head, T);
     if (!ok) return fail("cuTensorMapEncodeTiled failed for activation buffers");
     e->finalized = true;
     return 0;
@@ -357,7 +360,7 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
         if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, T, 3 * d, d, L.bqkv, nullptr, e->to_qkv, BK_EPI_BIAS)) return -1;
         {
             KTimer t(e, BK_K_ATTN);
-            CK(launch_attention(e->qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
+            CK(launch_attention(e->ta_qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
             e->launch_count++;
         }
         if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, T, d, d, L.bo, &e->tr_x, e->to_pre, BK_EPI_BIAS_RESID)) return -1;

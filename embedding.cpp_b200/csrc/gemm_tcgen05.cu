@@ -391,7 +391,7 @@ static PFN_encodeTiled get_encode_fn() {
 }
 
 bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_t rows, uint64_t row_stride_bytes,
-                      uint32_t box_inner, uint32_t box_rows) {
+                      uint32_t box_inner, uint32_t box_rows, int swizzle_bytes) {
     PFN_encodeTiled enc = get_encode_fn();
     if (!enc) return false;
     cuuint64_t dims[2] = {inner, rows};
@@ -399,7 +399,8 @@ bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_
     cuuint32_t box[2] = {box_inner, box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }

@@ -31,9 +31,9 @@ void gemm_pick_tile(int M, int N, int num_sms, int *bn, int *cg);
 // tmRes may be null unless epi == BK_EPI_BIAS_RESID.  Rows >= the maps' row count are never written.
 cudaError_t launch_gemm(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap *tmRes,
                         const GemmParams &p, int num_sms, cudaStream_t st, int force_bn = 0, int force_cg = 0);
-// 2-D f16 row-major tensor map (inner = contiguous dim) with 128-byte swizzle
+// 2-D f16 row-major tensor map (inner = contiguous dim) with 128-byte (or 64-byte) swizzle
 bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_t rows, uint64_t row_stride_bytes,
-                      uint32_t box_inner, uint32_t box_rows);
+                      uint32_t box_inner, uint32_t box_rows, int swizzle_bytes = 128);
 // y[i] = the epilogue's GELU of x[i] (tests)
 cudaError_t launch_gelu_test(const float *x, float *y, int n, cudaStream_t st);
 
@@ -57,9 +57,11 @@ cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *be
                           __half *y, __half *yq, int qmode, cudaStream_t st);
 cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, int n_seq, int d, float *out, cudaStream_t st);
 
-// ---- attention.cu ---------------------------------------------------------------------------
-// qkv [T][3d] f16 (Q | K | V along the row), out [T][d] f16; one sentence = rows cu[s]..cu[s+1]
-cudaError_t launch_attention(const __half *qkv, const int32_t *cu_seqlens, int n_seq, int max_len, int d, int n_head,
+// ---- attention_tc.cu ------------------------------------------------------------------------
+// qkv [T][3d] f16 (Q | K | V along the row) read through tmQKV (make_tmap_attention), out [T][d] f16;
+// one sentence = rows cu[s]..cu[s+1], at most 512 tokens; head size 32 or 64
+bool make_tmap_attention(CUtensorMap *tm, const void *qkv, int d, int n_head, uint64_t rows);
+cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens, int n_seq, int max_len, int d, int n_head,
                              __half *out, int qmode, cudaStream_t st);
 
 // ---- dequant.cu -----------------------------------------------------------------------------

@@ -118,7 +118,9 @@ BK_API int bk_test_attention(int device, int32_t n_seq, const int32_t *lens, int
     if (upload_lens(lens, n_seq, dL, dC, dPos, &T, &mx, 0)) return -1;
     TCK(dQ.alloc((size_t)T * 3 * d * 2)); TCK(dO.alloc((size_t)T * d * 2));
     TCK(cudaMemcpy(dQ.p, qkv, (size_t)T * 3 * d * 2, cudaMemcpyHostToDevice));
-    TCK(launch_attention(dQ.as<__half>(), dC.as<int32_t>(), n_seq, mx, d, n_head, dO.as<__half>(), qmode, 0));
+    CUtensorMap tmQ;
+    if (!make_tmap_attention(&tmQ, dQ.p, d, n_head, (uint64_t)T)) { fprintf(stderr, "bk_test_attention: cuTensorMapEncodeTiled failed\n"); return -1; }
+    TCK(launch_attention(tmQ, dC.as<int32_t>(), n_seq, mx, d, n_head, dO.as<__half>(), qmode, 0));
     TCK(cudaDeviceSynchronize());
     TCK(cudaMemcpy(out, dO.p, (size_t)T * d * 2, cudaMemcpyDeviceToHost));
     return 0;
