@@ -275,6 +275,7 @@ def main():
     ap.add_argument("--ref-sentences", type=int, default=2, help="reference arm: sentences per step")
     ap.add_argument("--cpu-baseline-sentences", type=int, default=12)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--latency-calls", type=int, default=200, help="timed bert_eval calls of the batch-1 latency leg")
     ap.add_argument("--legs", default="all", choices=["all", "value"], help="value: device-resident leg only (ncu captures)")
     ap.add_argument("--ref-threads", type=int, default=0, help="reference / cpu_baseline threads (0 = min(host cores, 32))")
     args = ap.parse_args()
@@ -352,6 +353,25 @@ def main():
     e2e_value = total_sent * args.steps / t_e2e
     same = bool(np.array_equal(out, out_dev))
     unit_norm = bool(np.allclose(np.linalg.norm(out, axis=1), 1.0, atol=1e-3))
+
+    # ---------------- leg 3: batch-1 latency through bert_eval (BASELINE.json: "p50 batch-1 latency") ----
+    latency = None
+    if dist.rank == 0:
+        one = np.ascontiguousarray(batch[0][:128] if seq_len == 0 else batch[0], np.int32)
+        emb1 = np.zeros(hp.n_embd, np.float32)
+        tp1 = one.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
+        ep1 = emb1.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+        for _ in range(20):
+            lib.bert_eval(model.ctx, 1, tp1, len(one), ep1)
+        ts = []
+        for _ in range(args.latency_calls):
+            t0 = time.perf_counter()
+            lib.bert_eval(model.ctx, 1, tp1, len(one), ep1)      # host ids in, host embedding out, one sentence
+            ts.append(time.perf_counter() - t0)
+        ts = np.sort(np.array(ts)) * 1e3
+        latency = {"p50_ms": float(ts[len(ts) // 2]), "p90_ms": float(ts[int(len(ts) * 0.9)]), "min_ms": float(ts[0]),
+                   "calls": int(len(ts)), "tokens": int(len(one)),
+                   "api": "bert_eval (one sentence, host buffers in/out; launch plan replayed as a CUDA graph)"}
     model.close()
 
     # ---------------- roofline of the dominant kernel -------------------------------------------------
@@ -393,6 +413,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": "embeddings/s", "h2d_bytes_per_step": int(4 * T + 4 * n_sent),
                 "d2h_bytes_per_step": int(4 * n_sent * hp.n_embd), "api": "bert_eval_batch (build/libbert.so via ctypes), host pointers in/out",
                 "matches_device_leg": same, "unit_norm": unit_norm},
+        "latency_batch1": latency,
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "model_tflops_per_gpu": model_tflops, "model_frac_of_peak": model_tflops / peaks["tflops_sustained"],
     }

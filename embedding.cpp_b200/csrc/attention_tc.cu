@@ -295,8 +295,14 @@ static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_se
     const int Lk64 = (max_len + 63) & ~63;
     const int qk = (kAttQ + Lk64) * DH * 2;
     const size_t smem = (size_t)(qk > 2 * kAttQ * 128 ? qk : 2 * kAttQ * 128) + (size_t)Lk64 * DH * 2 + 1024 /*align*/ + 128 + (size_t)G * 128 * 4;
-    cudaError_t err = cudaFuncSetAttribute(attention_tc_kernel<DH, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (err != cudaSuccess) return err;
+    static bool attr_set[64] = {false};  // per kernel instance and device (the attribute is per device)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        cudaError_t err = cudaFuncSetAttribute(attention_tc_kernel<DH, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (err != cudaSuccess) return err;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
     dim3 grid((max_len + kAttQ - 1) / kAttQ, n_head, n_seq);
     const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934: 1.0f/sqrt((float)dh) evaluated in double
     attention_tc_kernel<DH, G><<<grid, 32 + 128 * G, smem, st>>>(tm, cu, d, out, qmode, scale);

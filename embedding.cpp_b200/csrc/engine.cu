@@ -106,6 +106,11 @@ struct bk_engine {
     // hidden-state capture (tests)
     bool keep_hidden = false;
     __half *hidden = nullptr;  // [n_layer+1][cap_tokens][d]
+    // CUDA graphs of the launch plan for small batches (latency path): key = (T, n_seq, max_len)
+    struct GraphEntry { int T, n_seq, max_len; cudaGraphExec_t exec; uint64_t last_use; };
+    std::vector<GraphEntry> graphs;
+    uint64_t graph_clock = 0;
+    int graph_max_tokens = 4096;  // BERT_B200_GRAPH_TOKENS; 0 disables
     // timing
     std::vector<cudaEvent_t> ev;
     std::vector<int> ev_kind;
@@ -183,6 +188,7 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     e->cap_seqs = cap_seqs;
     e->num_sms = prop.multiProcessorCount;
     e->qmode = hp->wtype == BK_Q4_0 ? 1 : hp->wtype == BK_Q4_1 ? 2 : 0;
+    if (const char *v = getenv("BERT_B200_GRAPH_TOKENS")) e->graph_max_tokens = atoi(v);
     e->tens.resize(5 + 16 * (size_t)hp->n_layer);
     e->layers.resize(hp->n_layer);
     if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) { fail("cudaStreamCreate failed"); delete e; return nullptr; }
@@ -202,6 +208,7 @@ BK_API void bk_engine_destroy(bk_engine *e) {
     if (e->h_lens) cudaFreeHost(e->h_lens);
     if (e->h_out) cudaFreeHost(e->h_out);
     for (auto ev : e->ev) cudaEventDestroy(ev);
+    for (auto &g : e->graphs) cudaGraphExecDestroy(g.exec);
     if (e->st) cudaStreamDestroy(e->st);
     delete e;
 }
@@ -388,6 +395,38 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
     return 0;
 }
 
+// the same launch sequence captured once per (T, n_seq, max_len) and replayed (kernel arguments -- sizes, tensor
+// maps, engine-owned device pointers -- are identical for equal keys); least-recently-used of 32 shapes is evicted
+int forward_graph(bk_engine *e, int T, int n_seq, int max_len) {
+    e->graph_clock++;
+    for (auto &g : e->graphs)
+        if (g.T == T && g.n_seq == n_seq && g.max_len == max_len) {
+            g.last_use = e->graph_clock;
+            CK(cudaGraphLaunch(g.exec, e->st));
+            e->launch_count += 4 + 7 * e->hp.n_layer;
+            return 0;
+        }
+    cudaGraph_t graph = nullptr;
+    CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
+    const int rc = forward_device(e, e->d_tokens, e->d_lens, T, n_seq, max_len, e->d_out);
+    const cudaError_t ce = cudaStreamEndCapture(e->st, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (ce != cudaSuccess) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) return fail("cudaGraphInstantiate: %s", cudaGetErrorString(ie));
+    if (e->graphs.size() >= 32) {
+        size_t lru = 0;
+        for (size_t i = 1; i < e->graphs.size(); i++) if (e->graphs[i].last_use < e->graphs[lru].last_use) lru = i;
+        cudaGraphExecDestroy(e->graphs[lru].exec);
+        e->graphs.erase(e->graphs.begin() + (long)lru);
+    }
+    e->graphs.push_back({T, n_seq, max_len, exec, e->graph_clock});
+    CK(cudaGraphLaunch(exec, e->st));
+    return 0;
+}
+
 int check_batch(bk_engine *e, const int32_t *lens, int n_seq, int *T_out, int *maxlen_out) {
     if (!e || !e->finalized) return fail("engine not finalized");
     if (n_seq < 1 || n_seq > e->cap_seqs) return fail("n_seq %d outside 1..%d", n_seq, e->cap_seqs);
@@ -451,7 +490,10 @@ BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t 
     CK(cudaMemcpyAsync(e->d_tokens, e->h_tokens, (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
     CK(cudaMemcpyAsync(e->d_lens, e->h_lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
     e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
-    if (forward_device(e, e->d_tokens, e->d_lens, T, n_seq, mx, e->d_out)) return -1;
+    if (T <= e->graph_max_tokens && !e->keep_hidden && !e->timing) {
+        // small batch: the 3 + 7*n_layer + 1 launches cost more host time than GPU time -> replay a captured graph
+        if (forward_graph(e, T, n_seq, mx)) return -1;
+    } else if (forward_device(e, e->d_tokens, e->d_lens, T, n_seq, mx, e->d_out)) return -1;
     const size_t ob = (size_t)n_seq * e->hp.n_embd * 4;
     CK(cudaMemcpyAsync(e->h_out, e->d_out, ob, cudaMemcpyDeviceToHost, e->st));
     CK(cudaStreamSynchronize(e->st));

@@ -327,8 +327,14 @@ template <int BN, int CG>
 static cudaError_t launch_cfg(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap &tmRes,
                               const GemmParams &p, int num_sms, cudaStream_t st) {
     using Cfg = GemmCfg<BN, CG>;
-    cudaError_t err = cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (err != cudaSuccess) return err;
+    static bool attr_set[64] = {false};  // per kernel instance and device (the attribute is per device)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        cudaError_t err = cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (err != cudaSuccess) return err;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
     const int bi = brow_index(Cfg::B_ROWS);
     if (bi < 0) return cudaErrorInvalidValue;
     const int m_tiles = (p.M + GEMM_BLOCK_M * CG - 1) / (GEMM_BLOCK_M * CG), n_tiles = (p.N + BN - 1) / BN;

@@ -74,6 +74,23 @@ def test_batch_equals_single_and_is_deterministic(binding, make_model):
     m.close()
 
 
+def test_graph_replay_equals_direct_launches(binding, make_model, monkeypatch):
+    """small batches replay the launch plan as a CUDA graph (latency path); results must be bit-identical to
+    direct launches, also when the same shape is replayed with other tokens and when shapes alternate"""
+    path = make_model("mini64", "q4_1", seed=43)
+    rng = np.random.default_rng(11)
+    batches = [[rand_tokens(rng, 500, int(L)) for L in lens] for lens in ([128], [128], [5, 77, 300], [128], [5, 77, 300], [1])]
+    m = binding.BertB200(path)                         # graphs on (default)
+    got = [m.eval_batch(b) for b in batches]
+    m.close()
+    monkeypatch.setenv("BERT_B200_GRAPH_TOKENS", "0")  # graphs off
+    m = binding.BertB200(path)
+    want = [m.eval_batch(b) for b in batches]
+    m.close()
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+
+
 def test_hidden_states_vs_oracle(binding, orc, make_model):
     """per-layer intermediates: localises an error to a layer instead of only seeing the pooled output"""
     path = make_model("mini64", "f16", seed=41)
