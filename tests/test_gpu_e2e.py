@@ -91,6 +91,26 @@ def test_graph_replay_equals_direct_launches(binding, make_model, monkeypatch):
         assert np.array_equal(g, w)
 
 
+def test_multi_gpu_in_process_equals_single(binding, make_model, monkeypatch):
+    """one bert_ctx spread over 2 GPUs (worker thread per GPU, host gather) returns what one GPU returns"""
+    lib = binding.load_library()
+    if lib.bk_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    path = make_model("mini64", "f16", seed=44)
+    rng = np.random.default_rng(12)
+    batch = [rand_tokens(rng, 500, int(L)) for L in rng.integers(1, 512, 300)]
+    monkeypatch.setenv("BERT_B200_MB_TOKENS", "4096")   # several micro-batches per GPU
+    monkeypatch.setenv("BERT_B200_DEVICES", "0")
+    m = binding.BertB200(path)
+    one = m.eval_batch(batch)
+    m.close()
+    monkeypatch.setenv("BERT_B200_DEVICES", "0,1")
+    m = binding.BertB200(path)
+    two = m.eval_batch(batch)
+    m.close()
+    assert np.array_equal(one, two)
+
+
 def test_hidden_states_vs_oracle(binding, orc, make_model):
     """per-layer intermediates: localises an error to a layer instead of only seeing the pooled output"""
     path = make_model("mini64", "f16", seed=41)
