@@ -229,6 +229,11 @@ __device__ __forceinline__ void tma_load_2d_pair_e(void *smem_dst, const void *t
                  ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(bar_addr), "r"(c0), "r"(c1)
                  : "memory");
 }
+__device__ __forceinline__ void bulk_load_1d_e(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+    asm volatile(BK_ELECT_PROLOGUE "@e cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n\t}"
+                 ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 template <int kCG>
 __device__ __forceinline__ void umma_f16_e(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     if (kCG == 1)

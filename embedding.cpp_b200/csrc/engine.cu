@@ -52,6 +52,7 @@ struct HostTensor {  // device copy of one GGUF tensor in its storage type
 
 struct Layer {
     __half *wqkv = nullptr, *wo = nullptr, *w1 = nullptr, *w2 = nullptr;
+    uint8_t *pqkv = nullptr, *po = nullptr, *p1 = nullptr, *p2 = nullptr;  // Q4 models: the same matrices still packed (re-tiled GGUF blocks)
     float *bqkv = nullptr;
     const float *bo = nullptr, *b1 = nullptr, *b2 = nullptr, *ln1g = nullptr, *ln1b = nullptr, *ln2g = nullptr, *ln2b = nullptr;
     WeightMaps tm_wqkv, tm_wo, tm_w1, tm_w2;
@@ -111,6 +112,10 @@ struct bk_engine {
     std::vector<GraphEntry> graphs;
     uint64_t graph_clock = 0;
     int graph_max_tokens = 4096;  // BERT_B200_GRAPH_TOKENS; 0 disables
+    // Q4 models: batches of up to this many tokens (the latency regime) run the GEMMs from the packed weights (decoded in shared memory,
+    // only Q4 bytes cross HBM: weight traffic dominates there); larger ones use the f16 operand copies, where
+    // weights are < 2% of the bytes moved and the decode would compete with the epilogue for issue slots.
+    int q4_smem_tokens = 1024;    // BERT_B200_Q4_SMEM_TOKENS; -1 = always, 0 = never
     // timing
     std::vector<cudaEvent_t> ev;
     std::vector<int> ev_kind;
@@ -189,6 +194,7 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     e->num_sms = prop.multiProcessorCount;
     e->qmode = hp->wtype == BK_Q4_0 ? 1 : hp->wtype == BK_Q4_1 ? 2 : 0;
     if (const char *v = getenv("BERT_B200_GRAPH_TOKENS")) e->graph_max_tokens = atoi(v);
+    if (const char *v = getenv("BERT_B200_Q4_SMEM_TOKENS")) e->q4_smem_tokens = atoi(v);
     e->tens.resize(5 + 16 * (size_t)hp->n_layer);
     e->layers.resize(hp->n_layer);
     if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) { fail("cudaStreamCreate failed"); delete e; return nullptr; }
@@ -201,7 +207,10 @@ BK_API void bk_engine_destroy(bk_engine *e) {
     cudaSetDevice(e->device);
     if (e->st) cudaStreamSynchronize(e->st);
     for (auto &t : e->tens) if (t.dev) cudaFree(t.dev);
-    for (auto &l : e->layers) { cudaFree(l.wqkv); cudaFree(l.wo); cudaFree(l.w1); cudaFree(l.w2); cudaFree(l.bqkv); }
+    for (auto &l : e->layers) {
+        cudaFree(l.wqkv); cudaFree(l.wo); cudaFree(l.w1); cudaFree(l.w2); cudaFree(l.bqkv);
+        cudaFree(l.pqkv); cudaFree(l.po); cudaFree(l.p1); cudaFree(l.p2);
+    }
     void *bufs[] = {e->d_tokens, e->d_lens, e->d_cu, e->d_pos, e->x, e->xq, e->qkv, e->att, e->pre, e->y, e->yq, e->h, e->d_out, e->hidden, e->sg_tokens, e->sg_lens, e->sg_out};
     for (void *b : bufs) if (b) cudaFree(b);
     if (e->h_tokens) cudaFreeHost(e->h_tokens);
@@ -272,6 +281,27 @@ BK_API int bk_engine_finalize(bk_engine *e) {
             CK(launch_weight_to_f16(w.dev, w.type, d, d, L.wqkv + (size_t)i * d * d, e->st));
             CK(cudaMemcpyAsync(L.bqkv + (size_t)i * d, e->tens[L_SLOT(l, qkvb[i])].dev, (size_t)d * 4, cudaMemcpyDeviceToDevice, e->st));
         }
+        if (e->qmode) {
+            const int wt = hp.wtype;
+            const size_t bb2 = wt == BK_Q4_0 ? 36 : 40;
+            CK(cudaMalloc(&L.pqkv, (size_t)3 * d * (d / 64) * bb2));
+            CK(cudaMalloc(&L.po, (size_t)d * (d / 64) * bb2));
+            CK(cudaMalloc(&L.p1, (size_t)f * (d / 64) * bb2));
+            CK(cudaMalloc(&L.p2, (size_t)d * (f / 64) * bb2));
+            for (int i = 0; i < 3; i++) {
+                const HostTensor &w = e->tens[L_SLOT(l, qkvw[i])];
+                if (w.type != wt) return fail("layer %d: mixed weight types", l);
+                CK(launch_q4_retile(w.dev, wt, (int)d, (int)d, L.pqkv, 3 * (int)d, i * (int)d, e->st));
+            }
+            const int ws[3] = {S_OW, S_W1, S_W2};
+            uint8_t *dst[3] = {L.po, L.p1, L.p2};
+            const int rows[3] = {(int)d, (int)f, (int)d}, ks[3] = {(int)d, (int)d, (int)f};
+            for (int i = 0; i < 3; i++) {
+                const HostTensor &w = e->tens[L_SLOT(l, ws[i])];
+                if (w.type != wt) return fail("layer %d: mixed weight types", l);
+                CK(launch_q4_retile(w.dev, wt, rows[i], ks[i], dst[i], rows[i], 0, e->st));
+            }
+        }
         { const HostTensor &w = e->tens[L_SLOT(l, S_OW)]; CK(launch_weight_to_f16(w.dev, w.type, d, d, L.wo, e->st)); }
         { const HostTensor &w = e->tens[L_SLOT(l, S_W1)]; CK(launch_weight_to_f16(w.dev, w.type, f, d, L.w1, e->st)); }
         { const HostTensor &w = e->tens[L_SLOT(l, S_W2)]; CK(launch_weight_to_f16(w.dev, w.type, d, f, L.w2, e->st)); }
@@ -331,11 +361,12 @@ struct KTimer {  // brackets one kernel class with two events when timing is on
     }
 };
 
-int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const WeightMaps &W, int M, int N, int K, const float *bias,
+int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const WeightMaps &W, const uint8_t *packed, int M, int N, int K, const float *bias,
              const CUtensorMap *tmRes, const CUtensorMap &tmOut, int epi) {
     KTimer t(e, kind);
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.bias = bias; p.epi = epi;
+    if (e->qmode && packed && K % 64 == 0 && (e->q4_smem_tokens < 0 || M <= e->q4_smem_tokens)) { p.wq = packed; p.wq_type = e->hp.wtype; }
     CK(launch_gemm(tmA, W, tmOut, tmRes, p, e->num_sms, e->st));
     e->launch_count++;
     return 0;
@@ -364,21 +395,21 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
     if (e->keep_hidden) CK(cudaMemcpyAsync(e->hidden, e->x, (size_t)T * d * 2, cudaMemcpyDeviceToDevice, e->st));
     for (int l = 0; l < hp.n_layer; l++) {
         Layer &L = e->layers[l];
-        if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, T, 3 * d, d, L.bqkv, nullptr, e->to_qkv, BK_EPI_BIAS)) return -1;
+        if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, L.pqkv, T, 3 * d, d, L.bqkv, nullptr, e->to_qkv, BK_EPI_BIAS)) return -1;
         {
             KTimer t(e, BK_K_ATTN);
             CK(launch_attention(e->ta_qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
             e->launch_count++;
         }
-        if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, T, d, d, L.bo, &e->tr_x, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
+        if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, L.po, T, d, d, L.bo, &e->tr_x, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
         {
             KTimer t(e, BK_K_ADD_LN);
             CK(launch_add_ln(e->pre, L.ln1g, L.ln1b, T, d, hp.eps, e->y, e->yq, q, e->st));
             e->launch_count++;
         }
         const int epi1 = q == 0 ? BK_EPI_BIAS_GELU : q == 1 ? BK_EPI_BIAS_GELU_Q8_0 : BK_EPI_BIAS_GELU_Q8_1;
-        if (run_gemm(e, BK_K_GEMM_FF1, e->tm_y, L.tm_w1, T, f, d, L.b1, nullptr, e->to_h, epi1)) return -1;
-        if (run_gemm(e, BK_K_GEMM_FF2, e->tm_h, L.tm_w2, T, d, f, L.b2, &e->tr_y, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
+        if (run_gemm(e, BK_K_GEMM_FF1, e->tm_y, L.tm_w1, L.p1, T, f, d, L.b1, nullptr, e->to_h, epi1)) return -1;
+        if (run_gemm(e, BK_K_GEMM_FF2, e->tm_h, L.tm_w2, L.p2, T, d, f, L.b2, &e->tr_y, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
         {
             KTimer t(e, BK_K_ADD_LN);
             CK(launch_add_ln(e->pre, L.ln2g, L.ln2b, T, d, hp.eps, e->x, e->xq, q, e->st));

@@ -35,7 +35,6 @@ namespace bk {
 
 constexpr int kGemmThreads = 640;
 constexpr int kEpiWarp0 = 4;
-constexpr int kEpiThreads = 512;   // two teams
 constexpr int kTeamThreads = 256;
 constexpr int kSmemLimit = 227 * 1024;
 constexpr int kBoxBytes = GEMM_BLOCK_M * GEMM_OUT_BOX_N * 2;  // 16 KB
@@ -43,12 +42,21 @@ constexpr int kBoxBytes = GEMM_BLOCK_M * GEMM_OUT_BOX_N * 2;  // 16 KB
 // CG = 1: one CTA per tile (tcgen05.mma.cta_group::1, M = 128).  CG = 2: a CTA pair (cluster of 2) per 256 x BN
 // tile: each CTA holds its own 128 rows of A and BN/2 rows of W, the leader issues cta_group::2 MMAs that read
 // both CTAs' shared memory, so every CTA streams (128 + BN/2) instead of (128 + BN) operand rows per K block.
-template <int BN, int CG>
+// WQ = 0: W is an f16 [N][K] operand copy fetched by TMA.  WQ = 1 / 2: W stays in its GGUF Q4_0 / Q4_1 blocks in
+// HBM (re-tiled at load so that the two 32-weight blocks of 64 consecutive K of BN consecutive rows are
+// contiguous); the producer streams the packed bytes with 1-D bulk copies and eight decode warps expand them to
+// f16 directly into the swizzled UMMA operand tile in shared memory (block layout ggml-quants.h:10-55, decode
+// ggml-quants.c:1074-1113) -- only packed weight bytes cross HBM / L2.  One epilogue team instead of two.
+template <int BN, int CG, int WQ>
 struct GemmCfg {
+    static_assert(WQ == 0 || CG == 1, "in-smem Q4 decode is built for one-CTA tiles");
     static constexpr int A_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;  // 16 KB
     static constexpr int B_ROWS = BN / CG;                           // W rows this CTA loads per K block
     static constexpr int B_BYTES = B_ROWS * GEMM_BLOCK_K * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int PK_ROWB = WQ == 1 ? 36 : WQ == 2 ? 40 : 0;  // packed bytes of 64 weights of one row
+    static constexpr int PK_BYTES = (B_ROWS * PK_ROWB + 1023) / 1024 * 1024;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + PK_BYTES;
+    static constexpr int NTEAMS = WQ ? 1 : 2;                        // epilogue teams of 8 warps
     static constexpr int NBOX = BN / GEMM_OUT_BOX_N;
     static constexpr int OUT_BYTES = NBOX * kBoxBytes;
     static constexpr int BAR_BYTES = 512;
@@ -58,16 +66,76 @@ struct GemmCfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024 + BAR_BYTES;
     static_assert(BN % 64 == 0 && BN <= 256, "tile width");
     static_assert(STAGES >= 3, "operand ring too shallow");
-    static_assert((2 * STAGES + 4 + 2 * NBOX) * 8 + 8 <= BAR_BYTES, "barrier area");
+    static_assert((3 * STAGES + 4 + 2 * NBOX) * 8 + 8 <= BAR_BYTES, "barrier area");
 };
 
-template <int BN, int CG>
+// 64 consecutive weights of one row = two GGUF blocks (w = the row's 36 / 40 packed bytes, 4-byte aligned) -> 64
+// halves o[0..7].  Q4_0: (q - 8) * d, Q4_1: q * d + m; element j of a block is the low nibble of byte j, element
+// j + 16 the high nibble (ggml-quants.c:1074-1113).  Bit-identical to the load-time expansion (rowwise.cu
+// load_row8 + one f16 rounding): Q4_0 products are exact before the single f16 rounding; Q4_1 goes through the
+// same fp32 fma.
+template <int WQ>
+__device__ __forceinline__ void q4_decode_row(const uint32_t *w, uint4 (&o)[8]) {
+    constexpr int NW = WQ == 1 ? 9 : 10;
+    uint32_t x[NW];
+#pragma unroll
+    for (int i = 0; i < NW; i++) x[i] = w[i];
+#pragma unroll
+    for (int blk = 0; blk < 2; blk++) {
+        uint32_t qs[4];
+        uint32_t dm;  // d in the low half (and m in the high half for Q4_1)
+        if (WQ == 1) {
+            if (blk == 0) {  // bytes 0..17: d | 16 nibble bytes starting at byte 2
+                dm = x[0] & 0xFFFFu;
+#pragma unroll
+                for (int i = 0; i < 4; i++) qs[i] = __funnelshift_r(x[i], x[i + 1], 16);
+            } else {         // bytes 18..35
+                dm = x[4] >> 16;
+#pragma unroll
+                for (int i = 0; i < 4; i++) qs[i] = x[5 + i];
+            }
+        } else {
+            dm = x[5 * blk];
+#pragma unroll
+            for (int i = 0; i < 4; i++) qs[i] = x[5 * blk + 1 + i];
+        }
+        const __half dh = __ushort_as_half((unsigned short)(dm & 0xFFFFu));
+        uint32_t lo[8], hi[8];  // half2 words: K 0..15 from the low nibbles, K 16..31 from the high nibbles
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t l = qs[i] & 0x0F0F0F0Fu, h = (qs[i] >> 4) & 0x0F0F0F0Fu;
+            // bytes [v, 0x64] = the half 1024 + v
+            const uint32_t l01 = __byte_perm(l, 0x64646464u, 0x4140), l23 = __byte_perm(l, 0x64646464u, 0x4342);
+            const uint32_t h01 = __byte_perm(h, 0x64646464u, 0x4140), h23 = __byte_perm(h, 0x64646464u, 0x4342);
+            if (WQ == 1) {
+                const __half2 d2 = __half2half2(dh), off = __float2half2_rn(1032.f);
+                auto f = [&](uint32_t v) { __half2 r = __hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&v), off), d2); return *reinterpret_cast<uint32_t *>(&r); };
+                lo[2 * i] = f(l01); lo[2 * i + 1] = f(l23); hi[2 * i] = f(h01); hi[2 * i + 1] = f(h23);
+            } else {
+                const float dd = __half2float(dh), mm = __half2float(__ushort_as_half((unsigned short)(dm >> 16)));
+                const __half2 off = __float2half2_rn(1024.f);
+                auto f = [&](uint32_t v) {
+                    const float2 q = __half22float2(__hsub2(*reinterpret_cast<const __half2 *>(&v), off));
+                    return pack_h2(fmaf(q.x, dd, mm), fmaf(q.y, dd, mm));
+                };
+                lo[2 * i] = f(l01); lo[2 * i + 1] = f(l23); hi[2 * i] = f(h01); hi[2 * i + 1] = f(h23);
+            }
+        }
+        o[4 * blk + 0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        o[4 * blk + 1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+        o[4 * blk + 2] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        o[4 * blk + 3] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+    }
+}
+
+template <int BN, int CG, int WQ>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GemmParams p) {
-    using Cfg = GemmCfg<BN, CG>;
+    using Cfg = GemmCfg<BN, CG, WQ>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int NBOX = Cfg::NBOX;
+    constexpr int NTEAMS = Cfg::NTEAMS;
     constexpr int TILE_M = GEMM_BLOCK_M * CG;  // rows of one (pair) tile
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -79,7 +147,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint64_t *tempty_bar = tfull_bar + 2;       // [2] accumulator drained
     uint64_t *rfull_bar = tempty_bar + 2;       // [NBOX] residual box landed
     uint64_t *sfree_bar = rfull_bar + NBOX;     // [NBOX] store of this box has finished reading it
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sfree_bar + NBOX);
+    uint64_t *pkfull_bar = sfree_bar + NBOX;    // [STAGES] packed weight bytes landed (WQ only)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(pkfull_bar + STAGES);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -99,8 +168,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tma_prefetch_desc(&tmB);
         tma_prefetch_desc(&tmOut);
         if (has_resid) tma_prefetch_desc(&tmRes);
-        for (int i = 0; i < STAGES; i++) { mbar_init(&full_bar[i], CG); mbar_init(&empty_bar[i], 1); }   // full: one producer arrival per CTA
-        for (int i = 0; i < 2; i++) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], CG * kEpiThreads / 32); }
+        // full: one producer arrival per CTA (+ one per decode warp that writes rows of the W tile)
+        for (int i = 0; i < STAGES; i++) { mbar_init(&full_bar[i], CG + (WQ ? BN / 32 : 0)); mbar_init(&empty_bar[i], 1); mbar_init(&pkfull_bar[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], CG * NTEAMS * 8); }
         for (int i = 0; i < NBOX; i++) { mbar_init(&rfull_bar[i], 1); mbar_init(&sfree_bar[i], 1); }
         mbar_fence_init();
     }
@@ -121,14 +191,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int kb = 0; kb < num_kb; kb++) {
                 mbar_wait(&empty_bar[s], ph ^ 1);
                 uint8_t *sa = ring + s * Cfg::STAGE_BYTES, *sb = sa + Cfg::A_BYTES;
-                if (CG == 1) {
-                    mbar_expect_tx_e(&full_bar[s], Cfg::STAGE_BYTES);
+                if (WQ) {
+                    mbar_expect_tx_e(&full_bar[s], Cfg::A_BYTES);
+                    tma_load_2d_e(sa, &tmA, &full_bar[s], kb * GEMM_BLOCK_K, m0);
+                    const int rows = p.N - n0 < BN ? p.N - n0 : BN;  // multiple of 32 -> bytes multiple of 16
+                    const uint32_t bytes = (uint32_t)(rows * Cfg::PK_ROWB);
+                    mbar_expect_tx_e(&pkfull_bar[s], bytes);
+                    bulk_load_1d_e(sb + Cfg::B_BYTES, p.wq + ((size_t)kb * p.N + n0) * Cfg::PK_ROWB, bytes, &pkfull_bar[s]);
+                } else if (CG == 1) {
+                    mbar_expect_tx_e(&full_bar[s], Cfg::A_BYTES + Cfg::B_BYTES);
                     tma_load_2d_e(sa, &tmA, &full_bar[s], kb * GEMM_BLOCK_K, m0);
                     tma_load_2d_e(sb, &tmB, &full_bar[s], kb * GEMM_BLOCK_K, n0);
                 } else {
                     // both CTAs report to the leader's barrier: one arrival + this CTA's bytes each
                     const uint32_t lead_full = smem_u32(&full_bar[s]) & kPeerBitMask;
-                    mbar_arrive_expect_tx_cluster_e(lead_full, Cfg::STAGE_BYTES);
+                    mbar_arrive_expect_tx_cluster_e(lead_full, Cfg::A_BYTES + Cfg::B_BYTES);
                     tma_load_2d_pair_e(sa, &tmA, lead_full, kb * GEMM_BLOCK_K, m0);
                     tma_load_2d_pair_e(sb, &tmB, lead_full, kb * GEMM_BLOCK_K, n0);
                 }
@@ -176,7 +253,39 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 }
             }
         }
-    } else if (warp >= kEpiWarp0) {
+    } else if (WQ != 0 && warp >= kEpiWarp0 + 8) {
+        // ============================================================= Q4 decode warps (8 warps in NGRP groups)
+        // group g takes every NGRP-th K block, so NGRP stages are being decoded at any time; thread = one W row
+        constexpr int WPT = BN / 32 < 8 ? BN / 32 : 8;  // warps needed per W tile (one row per thread)
+        constexpr int NGRP = 8 / WPT;                    // tiles (K blocks) being decoded concurrently
+        const int dw = warp - (kEpiWarp0 + 8);
+        const int grp = dw / WPT;
+        const int r = (dw % WPT) * 32 + lane;  // row of the W tile
+        const uint32_t sw = (uint32_t)(r & 7);
+        int s = 0; uint32_t ph = 0;
+        uint32_t kcount = 0;
+        for (int t = unit; t < num_tiles; t += units) {
+            const int n0 = (t % n_tiles) * BN;
+            for (int kb = 0; kb < num_kb; kb++, kcount++) {
+                if ((int)(kcount % NGRP) == grp && r < BN) {  // warp-uniform (BN is a multiple of 32)
+                    uint8_t *sb = ring + s * Cfg::STAGE_BYTES + Cfg::A_BYTES;
+                    mbar_wait(&pkfull_bar[s], ph);
+                    uint4 o[8];
+                    if (n0 + r < p.N) q4_decode_row<WQ>(reinterpret_cast<const uint32_t *>(sb + Cfg::B_BYTES + r * Cfg::PK_ROWB), o);
+                    else {
+#pragma unroll
+                        for (int j = 0; j < 8; j++) o[j] = make_uint4(0, 0, 0, 0);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; j++) *reinterpret_cast<uint4 *>(sb + r * 128 + ((((uint32_t)j) ^ sw) << 4)) = o[j];
+                    fence_proxy_async_smem();  // generic-proxy writes -> visible to the MMA's operand fetch
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&full_bar[s]);
+                }
+                if (++s == STAGES) { s = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + 8 * NTEAMS) {
         // ========================================================================= epilogue
         const int ew = warp - kEpiWarp0;
         const int team = ew >> 3;         // boxes team, team+2, ...
@@ -184,7 +293,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int half = (ew >> 2) & 1;   // which 32 columns of the 64-column box
         const int r = quad * 32 + lane;   // row inside the tile
         const bool issuer = (ew & 7) == 0 && lane == 0;
-        const bool defer = (NBOX - team + 1) / 2 >= 2;  // this team owns >= 2 boxes: free box k when box k+1 is stored
+        const bool defer = (NBOX - team + NTEAMS - 1) / NTEAMS >= 2;  // this team owns >= 2 boxes: free box k when box k+1 is stored
         const uint32_t row_off = (uint32_t)r * 128u;
         const uint32_t sw = (uint32_t)(r & 7);      // 128-byte swizzle: 16-byte chunk index ^= row % 8
         int as = 0; uint32_t aph = 0;
@@ -202,13 +311,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 if (lane == 0) mbar_arrive_cluster(tempty_addr0 + 8u * as);
             }
 #pragma unroll 1
-            for (int b = team; b < NBOX; b += 2) {
+            for (int b = team; b < NBOX; b += NTEAMS) {
                 const int nb = n0 + b * GEMM_OUT_BOX_N;
                 const bool box_live = nb < p.N;
                 uint32_t acc[32];
                 tmem_ld_32x32(taddr + (uint32_t)(b * GEMM_OUT_BOX_N + half * 32), acc);
                 tmem_ld_wait();
-                if (b + 2 >= NBOX) {  // last read of this stage by this warp: hand the accumulator back to the MMA warp
+                if (b + NTEAMS >= NBOX) {  // last read of this stage by this warp: hand the accumulator back to the MMA warp
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster(tempty_addr0 + 8u * as);
@@ -323,15 +432,15 @@ void gemm_pick_tile(int M, int N, int num_sms, int *bn_out, int *cg_out) {
     *bn_out = best_bn; *cg_out = best_cg;
 }
 
-template <int BN, int CG>
+template <int BN, int CG, int WQ = 0>
 static cudaError_t launch_cfg(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap &tmRes,
                               const GemmParams &p, int num_sms, cudaStream_t st) {
-    using Cfg = GemmCfg<BN, CG>;
+    using Cfg = GemmCfg<BN, CG, WQ>;
     static bool attr_set[64] = {false};  // per kernel instance and device (the attribute is per device)
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        cudaError_t err = cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        cudaError_t err = cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, CG, WQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         if (err != cudaSuccess) return err;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
@@ -352,8 +461,10 @@ static cudaError_t launch_cfg(const CUtensorMap &tmA, const WeightMaps &W, const
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, CG>, tmA, W.tm[bi], tmOut, tmRes, p);
+    return cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, CG, WQ>, tmA, W.tm[bi], tmOut, tmRes, p);
 }
+
+static inline const CUtensorMap &tmR0(const CUtensorMap *tmRes, const CUtensorMap &tmOut) { return tmRes ? *tmRes : tmOut; }
 
 cudaError_t launch_gemm(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmOut, const CUtensorMap *tmRes,
                         const GemmParams &p, int num_sms, cudaStream_t st, int force_bn, int force_cg) {
@@ -365,6 +476,15 @@ cudaError_t launch_gemm(const CUtensorMap &tmA, const WeightMaps &W, const CUten
     gemm_pick_tile(p.M, p.N, num_sms, &bn, &cg);
     const int want_bn = force_bn ? force_bn : env_bn, want_cg = force_cg ? force_cg : env_cg;
     if (want_cg == 1 || want_cg == 2) cg = want_cg;
+    if (p.wq) {
+        // W stays packed (Q4_0 / Q4_1 blocks) and is decoded in shared memory: one-CTA tiles, 128 or 64 columns
+        if (p.wq_type != BK_Q4_0 && p.wq_type != BK_Q4_1) return cudaErrorInvalidValue;
+        // 128-column tiles unless that leaves SMs without a tile (small batches: more, narrower tiles)
+        const long tiles128 = (long)((p.M + GEMM_BLOCK_M - 1) / GEMM_BLOCK_M) * (p.N / 128);
+        const bool wide = p.N % 128 == 0 && want_bn != 64 && (want_bn == 128 || tiles128 >= num_sms);
+        if (p.wq_type == BK_Q4_0) return wide ? launch_cfg<128, 1, 1>(tmA, W, tmOut, tmR0(tmRes, tmOut), p, num_sms, st) : launch_cfg<64, 1, 1>(tmA, W, tmOut, tmR0(tmRes, tmOut), p, num_sms, st);
+        return wide ? launch_cfg<128, 1, 2>(tmA, W, tmOut, tmR0(tmRes, tmOut), p, num_sms, st) : launch_cfg<64, 1, 2>(tmA, W, tmOut, tmR0(tmRes, tmOut), p, num_sms, st);
+    }
     if (want_bn == 64 || ((want_bn == 128 || want_bn == 192 || want_bn == 256) && p.N % want_bn == 0)) bn = want_bn;
     const CUtensorMap &tmR = tmRes ? *tmRes : tmOut;
 #define BK_GEMM_CASE(BN_)                                                                                   \
@@ -416,6 +536,27 @@ bool make_weight_maps(WeightMaps *w, const void *base, int N, int K) {
     for (int i = 0; i < 6; i++)
         if (!make_tmap_f16_2d(&w->tm[i], base, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, GEMM_BLOCK_K, (uint32_t)kBRows[i])) return false;
     return true;
+}
+
+// ------------------------------------------------------------------------------ Q4 weight re-tiling
+// GGUF order [n][K/32 blocks] -> [K/64][n][2 blocks]: the 2 blocks (64 weights) of one row are bb2 = 36 / 40
+// contiguous bytes, and consecutive rows of the same 64-wide K slice follow each other, so a W tile of any
+// height is ONE contiguous 16-byte-aligned run for cp.async.bulk.  Same bytes, same count; done once at load.
+// The source may be one of several matrices stacked along N (Q, K, V): its rows go to rows n_off.. of N_total.
+__global__ void q4_retile_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, int n_rows, int K, int bb, int N_total, int n_off) {
+    const int kb = blockIdx.y, n = blockIdx.x * blockDim.y + threadIdx.y;
+    if (n >= n_rows) return;
+    const int bb2 = 2 * bb;
+    const uint8_t *s = src + ((size_t)n * (K / 32) + 2 * kb) * bb;
+    uint8_t *d = dst + ((size_t)kb * N_total + n_off + n) * bb2;
+    for (int i = threadIdx.x; i < bb2; i += blockDim.x) d[i] = s[i];
+}
+cudaError_t launch_q4_retile(const void *src, int wtype, int n_rows, int K, void *dst, int N_total, int n_off, cudaStream_t st) {
+    if ((wtype != BK_Q4_0 && wtype != BK_Q4_1) || K % 64 != 0 || N_total % 32 != 0 || n_off % 32 != 0) return cudaErrorInvalidValue;
+    dim3 block(8, 32), grid((n_rows + 31) / 32, K / 64);
+    q4_retile_kernel<<<grid, block, 0, st>>>(reinterpret_cast<const uint8_t *>(src), reinterpret_cast<uint8_t *>(dst), n_rows, K,
+                                             wtype == BK_Q4_0 ? 18 : 20, N_total, n_off);
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------ GELU alone (tests)

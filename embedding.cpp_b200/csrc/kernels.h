@@ -13,7 +13,13 @@ struct GemmParams {
     int M, N, K;
     const float *bias;  // [N]
     int epi;            // BK_EPI_*
+    // non-null: W is read as re-tiled Q4 blocks (launch_q4_retile) and decoded in shared memory; wq_type = BK_Q4_0 / BK_Q4_1
+    const uint8_t *wq = nullptr;
+    int wq_type = 0;
 };
+// GGUF Q4_0 / Q4_1 matrix [n_rows][K] (blocks along K) -> rows n_off.. of the K-slice-major tiling [K/64][N_total][2 blocks]
+// that the in-smem decode path streams; same bytes, same size
+cudaError_t launch_q4_retile(const void *src, int wtype, int n_rows, int K, void *dst, int N_total, int n_off, cudaStream_t st);
 constexpr int GEMM_BLOCK_M = 128;
 constexpr int GEMM_BLOCK_K = 64;
 constexpr int GEMM_OUT_BOX_N = 64;  // columns of one output / residual TMA box (128 B of f16, 128-byte swizzle)

@@ -64,8 +64,16 @@ BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint1
     }
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.bias = dB.as<float>(); p.epi = epi;
-    const int bn = (epi >> 8) & 0xFFF, cg = epi >> 20;  // tests may force the tile: epi | (BN << 8) | (CG << 20)
+    const int bn = (epi >> 8) & 0xFFF, cg = (epi >> 20) & 0xF;  // tests may force the tile: epi | (BN << 8) | (CG << 20)
+    const bool in_smem = (epi >> 28) & 1;                         // ... and, for Q4 weights, the in-smem decode path
     p.epi = epi & 0xFF;
+    DevBuf dWt;
+    if (in_smem) {
+        if (wtype != BK_Q4_0 && wtype != BK_Q4_1) { fprintf(stderr, "bk_test_gemm: in-smem decode needs Q4 weights\n"); return -1; }
+        TCK(dWt.alloc(wbytes));
+        TCK(launch_q4_retile(dWraw.p, wtype, N, K, dWt.p, N, 0, 0));
+        p.wq = dWt.as<uint8_t>(); p.wq_type = wtype;
+    }
     cudaEvent_t a, b;
     TCK(cudaEventCreate(&a)); TCK(cudaEventCreate(&b));
     TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn, cg));  // warm-up (also first-use setup)

@@ -91,6 +91,22 @@ def test_graph_replay_equals_direct_launches(binding, make_model, monkeypatch):
         assert np.array_equal(g, w)
 
 
+@pytest.mark.parametrize("ftype", ["q4_0", "q4_1"])
+def test_q4_packed_weight_path_equals_f16_copy_path(ftype, binding, make_model, monkeypatch):
+    """Q4 models: small batches run the projections from the packed GGUF blocks (decoded in shared memory), large
+    ones from f16 operand copies; both must give the same embeddings"""
+    path = make_model("mini64", ftype, seed=45)
+    rng = np.random.default_rng(13)
+    batch = [rand_tokens(rng, 500, int(L)) for L in (1, 128, 77, 512, 33)]
+    outs = []
+    for lim in ("-1", "0"):                              # always packed / never packed
+        monkeypatch.setenv("BERT_B200_Q4_SMEM_TOKENS", lim)
+        m = binding.BertB200(path)
+        outs.append(m.eval_batch(batch))
+        m.close()
+    assert np.array_equal(outs[0], outs[1])
+
+
 def test_multi_gpu_in_process_equals_single(binding, make_model, monkeypatch):
     """one bert_ctx spread over 2 GPUs (worker thread per GPU, host gather) returns what one GPU returns"""
     lib = binding.load_library()

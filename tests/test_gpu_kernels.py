@@ -117,6 +117,27 @@ def test_gemm_other_weight_storage(lib, gio, wname, wtype):
     assert (err <= 2e-3 * np.abs(ref) + 2e-3).all(), float(err.max())
 
 
+@pytest.mark.parametrize("wname,wtype", [("q4_0", 2), ("q4_1", 3)])
+@pytest.mark.parametrize("M,N,K,epi", [(200, 384, 768, 0), (1000, 2304, 768, 0), (333, 768, 3072, 1), (130, 96, 128, 2), (5, 3072, 768, 2)])
+def test_gemm_q4_decoded_in_shared_memory(lib, gio, wname, wtype, M, N, K, epi):
+    """W kept as GGUF Q4 blocks in device memory and decoded by the GEMM's decode warps: only packed bytes cross
+    HBM.  Must equal the path that expands W to f16 at load bit for bit (same values, same MMA K order)."""
+    rng = np.random.default_rng(M + N + K + wtype)
+    A = h(rng.standard_normal((M, K)) * 0.5)
+    Wf = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    raw = np.ascontiguousarray((gio.quantize_q4_0 if wtype == 2 else gio.quantize_q4_1)(Wf))
+    Wd = gio.dequantize(raw, wtype, (N, K)).astype(np.float16).astype(np.float32)
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float32)
+    resid = h(rng.standard_normal((M, N))) if epi == 1 else None
+    at_load, _ = run_gemm(lib, A, raw, wtype, N, bias, resid, epi)
+    in_smem, _ = run_gemm(lib, A, raw, wtype, N, bias, resid, epi | (1 << 28))
+    assert np.array_equal(at_load.view(np.uint16), in_smem.view(np.uint16))
+    if epi != 2:
+        ref = A.astype(np.float32) @ Wd.T + bias + (resid.astype(np.float32) if epi == 1 else 0)
+        err = np.abs(in_smem.astype(np.float32) - ref)
+        assert (err <= 2e-3 * np.abs(ref) + 2e-3).all(), float(err.max())
+
+
 @pytest.mark.parametrize("qepi,fn", [(3, "oracle_quant_q8_0_roundtrip"), (4, "oracle_quant_q8_1_roundtrip")])
 def test_gemm_gelu_q8_epilogue(lib, binding, orc, make_model, qepi, fn):
     M, N, K = 256, 512, 128
