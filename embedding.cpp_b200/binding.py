@@ -27,7 +27,7 @@ BERT_SYMBOLS = ["bert_load_from_file", "bert_free", "bert_encode", "bert_encode_
                 "bert_eval_batch", "bert_n_embd", "bert_n_max_tokens", "bert_vocab_id_to_token", "bert_model_quantize",
                 "bert_params_parse"]
 BK_SYMBOLS = ["bk_device_count", "bk_last_error", "bk_engine_create", "bk_engine_destroy", "bk_engine_set_tensor",
-              "bk_engine_finalize", "bk_engine_forward", "bk_engine_stage", "bk_engine_run_staged", "bk_engine_read_output",
+              "bk_engine_finalize", "bk_engine_forward", "bk_engine_submit", "bk_engine_collect", "bk_engine_stage", "bk_engine_run_staged", "bk_engine_read_output",
               "bk_engine_kernel_ms", "bk_engine_read_hidden", "bk_engine_set_keep_hidden", "bk_engine_launch_count", "bk_profiler_range",
               "bk_test_gemm", "bk_test_gelu", "bk_test_add_ln", "bk_test_attention", "bk_test_pool",
               "bk_tokenizer_create", "bk_tokenizer_destroy", "bk_tokenizer_encode"]

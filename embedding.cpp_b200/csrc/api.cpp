@@ -197,15 +197,35 @@ BERT_API void bert_eval_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n
     std::atomic<int> next{0};
     std::atomic<int> failed{0};
     auto worker = [&](int ei) {
+        // two micro-batches in flight per engine: while batch k runs on the GPU, batch k+1 is packed, uploaded and
+        // enqueued, and batch k-1's embeddings are scattered to the caller's rows
         bk_engine *e = ctx->engines[ei];
         std::vector<int32_t> toks, lens;
         std::vector<float> out;
-        for (;;) {
-            const int m = next.fetch_add(1);
-            if (m >= (int)mbs.size() || failed.load()) break;
+        int pending_mb[2] = {-1, -1};
+        auto collect = [&](int slot) -> bool {
+            const int m = pending_mb[slot];
+            if (m < 0) return true;
+            pending_mb[slot] = -1;
             const MicroBatch &mb = mbs[m];
             const int ns = mb.end - mb.begin;
-            toks.resize(mb.tokens); lens.resize(ns); out.resize((size_t)ns * d);
+            out.resize((size_t)ns * d);
+            if (bk_engine_collect(e, slot, out.data()) != 0) {
+                fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error());
+                failed.store(1);
+                return false;
+            }
+            for (int s = 0; s < ns; s++) memcpy(batch_embeddings[order[mb.begin + s]], out.data() + (size_t)s * d, (size_t)d * sizeof(float));
+            return true;
+        };
+        for (int k = 0;; k++) {
+            const int slot = k & 1;
+            const int m = next.fetch_add(1);
+            if (m >= (int)mbs.size() || failed.load()) break;
+            if (!collect(slot)) break;   // the slot's previous batch (k-2) must be read back before its buffers are reused
+            const MicroBatch &mb = mbs[m];
+            const int ns = mb.end - mb.begin;
+            toks.resize(mb.tokens); lens.resize(ns);
             int off = 0;
             for (int s = 0; s < ns; s++) {
                 const int b = order[mb.begin + s];
@@ -213,13 +233,16 @@ BERT_API void bert_eval_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n
                 memcpy(toks.data() + off, batch_tokens[b], (size_t)n_tokens[b] * sizeof(int32_t));
                 off += n_tokens[b];
             }
-            if (bk_engine_forward(e, toks.data(), lens.data(), ns, out.data()) != 0) {
+            if (bk_engine_submit(e, slot, toks.data(), lens.data(), ns) != 0) {
                 fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error());
                 failed.store(1);
                 break;
             }
-            for (int s = 0; s < ns; s++) memcpy(batch_embeddings[order[mb.begin + s]], out.data() + (size_t)s * d, (size_t)d * sizeof(float));
+            pending_mb[slot] = m;
+            if (!collect(slot ^ 1)) break;  // batch k-1: overlaps with batch k on the GPU
         }
+        collect(0);
+        collect(1);
     };
     const int n_workers = std::min<int>(n_eng, (int)mbs.size());
     if (n_workers <= 1) worker(0);

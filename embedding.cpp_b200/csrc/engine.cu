@@ -85,16 +85,21 @@ struct bk_engine {
     std::vector<Layer> layers;
 
     // workspaces
-    int32_t *d_tokens = nullptr, *d_lens = nullptr, *d_cu = nullptr, *d_pos = nullptr;
+    // two input/output slots: batch i+1 is staged, uploaded and enqueued while batch i's results are still being
+    // read back and scattered by the host (bk_engine_submit / bk_engine_collect)
+    int32_t *d_tokens2[2] = {nullptr, nullptr}, *d_lens2[2] = {nullptr, nullptr};
+    float *d_out2[2] = {nullptr, nullptr};
+    int32_t *h_tokens2[2] = {nullptr, nullptr}, *h_lens2[2] = {nullptr, nullptr};
+    float *h_out2[2] = {nullptr, nullptr};
+    cudaEvent_t slot_done[2] = {nullptr, nullptr};
+    int slot_nseq[2] = {0, 0};
+    int32_t *d_cu = nullptr, *d_pos = nullptr;
     __half *x = nullptr, *xq = nullptr, *qkv = nullptr, *att = nullptr, *pre = nullptr, *y = nullptr, *yq = nullptr, *h = nullptr;
-    float *d_out = nullptr;
     CUtensorMap tm_x, tm_att, tm_y, tm_h;  // A-operand maps (x/y point at the Q8-rounded copy for Q4 models)
     CUtensorMap to_qkv, to_pre, to_h;      // GEMM output maps (TMA stores), box {64, 128}
     CUtensorMap tr_x, tr_y;                // residual maps (unrounded x / y), box {64, 128}
     CUtensorMap ta_qkv;                    // attention's view of qkv: box {dh, 64 rows}
     // pinned staging
-    int32_t *h_tokens = nullptr, *h_lens = nullptr;
-    float *h_out = nullptr;
     // staged batch
     int st_T = 0, st_nseq = 0, st_maxlen = 0;  // last forward (hidden-state readback)
     // staged set (bench `value` leg): a whole job resident in HBM, cut into micro-batches of <= cap_tokens
@@ -108,7 +113,7 @@ struct bk_engine {
     bool keep_hidden = false;
     __half *hidden = nullptr;  // [n_layer+1][cap_tokens][d]
     // CUDA graphs of the launch plan for small batches (latency path): key = (T, n_seq, max_len)
-    struct GraphEntry { int T, n_seq, max_len; cudaGraphExec_t exec; uint64_t last_use; };
+    struct GraphEntry { int T, n_seq, max_len, slot; cudaGraphExec_t exec; uint64_t last_use; };
     std::vector<GraphEntry> graphs;
     uint64_t graph_clock = 0;
     int graph_max_tokens = 4096;  // BERT_B200_GRAPH_TOKENS; 0 disables
@@ -139,9 +144,16 @@ BK_API int bk_device_count(void) {
 static int engine_alloc(bk_engine *e) {
     const bk_hparams &hp = e->hp;
     const size_t T = (size_t)e->cap_tokens, d = hp.n_embd, f = hp.n_intermediate;
-    CK(cudaMalloc(&e->d_tokens, T * 4));
+    for (int sl = 0; sl < 2; sl++) {
+        CK(cudaMalloc(&e->d_tokens2[sl], T * 4));
+        CK(cudaMalloc(&e->d_lens2[sl], (size_t)e->cap_seqs * 4));
+        CK(cudaMalloc(&e->d_out2[sl], (size_t)e->cap_seqs * d * 4));
+        CK(cudaMallocHost(&e->h_tokens2[sl], T * 4));
+        CK(cudaMallocHost(&e->h_lens2[sl], (size_t)e->cap_seqs * 4));
+        CK(cudaMallocHost(&e->h_out2[sl], (size_t)e->cap_seqs * d * 4));
+        CK(cudaEventCreateWithFlags(&e->slot_done[sl], cudaEventDisableTiming));
+    }
     CK(cudaMalloc(&e->d_pos, T * 4));
-    CK(cudaMalloc(&e->d_lens, (size_t)e->cap_seqs * 4));
     CK(cudaMalloc(&e->d_cu, ((size_t)e->cap_seqs + 1) * 4));
     CK(cudaMalloc(&e->x, T * d * 2));
     CK(cudaMalloc(&e->qkv, T * 3 * d * 2));
@@ -153,10 +165,6 @@ static int engine_alloc(bk_engine *e) {
         CK(cudaMalloc(&e->xq, T * d * 2));
         CK(cudaMalloc(&e->yq, T * d * 2));
     }
-    CK(cudaMalloc(&e->d_out, (size_t)e->cap_seqs * d * 4));
-    CK(cudaMallocHost(&e->h_tokens, T * 4));
-    CK(cudaMallocHost(&e->h_lens, (size_t)e->cap_seqs * 4));
-    CK(cudaMallocHost(&e->h_out, (size_t)e->cap_seqs * d * 4));
     // the GEMM A operand may read (never store) rows past T inside the last 128-row tile: keep them finite
     CK(cudaMemsetAsync(e->x, 0, T * d * 2, e->st));
     CK(cudaMemsetAsync(e->qkv, 0, T * 3 * d * 2, e->st));  // attention's MMAs read up to 15 K/V rows past a sentence: finite
@@ -211,11 +219,15 @@ BK_API void bk_engine_destroy(bk_engine *e) {
         cudaFree(l.wqkv); cudaFree(l.wo); cudaFree(l.w1); cudaFree(l.w2); cudaFree(l.bqkv);
         cudaFree(l.pqkv); cudaFree(l.po); cudaFree(l.p1); cudaFree(l.p2);
     }
-    void *bufs[] = {e->d_tokens, e->d_lens, e->d_cu, e->d_pos, e->x, e->xq, e->qkv, e->att, e->pre, e->y, e->yq, e->h, e->d_out, e->hidden, e->sg_tokens, e->sg_lens, e->sg_out};
+    void *bufs[] = {e->d_tokens2[0], e->d_tokens2[1], e->d_lens2[0], e->d_lens2[1], e->d_out2[0], e->d_out2[1], e->d_cu, e->d_pos, e->x, e->xq, e->qkv,
+                    e->att, e->pre, e->y, e->yq, e->h, e->hidden, e->sg_tokens, e->sg_lens, e->sg_out};
     for (void *b : bufs) if (b) cudaFree(b);
-    if (e->h_tokens) cudaFreeHost(e->h_tokens);
-    if (e->h_lens) cudaFreeHost(e->h_lens);
-    if (e->h_out) cudaFreeHost(e->h_out);
+    for (int sl = 0; sl < 2; sl++) {
+        if (e->h_tokens2[sl]) cudaFreeHost(e->h_tokens2[sl]);
+        if (e->h_lens2[sl]) cudaFreeHost(e->h_lens2[sl]);
+        if (e->h_out2[sl]) cudaFreeHost(e->h_out2[sl]);
+        if (e->slot_done[sl]) cudaEventDestroy(e->slot_done[sl]);
+    }
     for (auto ev : e->ev) cudaEventDestroy(ev);
     for (auto &g : e->graphs) cudaGraphExecDestroy(g.exec);
     if (e->st) cudaStreamDestroy(e->st);
@@ -428,10 +440,10 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
 
 // the same launch sequence captured once per (T, n_seq, max_len) and replayed (kernel arguments -- sizes, tensor
 // maps, engine-owned device pointers -- are identical for equal keys); least-recently-used of 32 shapes is evicted
-int forward_graph(bk_engine *e, int T, int n_seq, int max_len) {
+int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len) {
     e->graph_clock++;
     for (auto &g : e->graphs)
-        if (g.T == T && g.n_seq == n_seq && g.max_len == max_len) {
+        if (g.T == T && g.n_seq == n_seq && g.max_len == max_len && g.slot == slot) {
             g.last_use = e->graph_clock;
             CK(cudaGraphLaunch(g.exec, e->st));
             e->launch_count += 4 + 7 * e->hp.n_layer;
@@ -439,7 +451,7 @@ int forward_graph(bk_engine *e, int T, int n_seq, int max_len) {
         }
     cudaGraph_t graph = nullptr;
     CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
-    const int rc = forward_device(e, e->d_tokens, e->d_lens, T, n_seq, max_len, e->d_out);
+    const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, max_len, e->d_out2[slot]);
     const cudaError_t ce = cudaStreamEndCapture(e->st, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (ce != cudaSuccess) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(ce));
@@ -453,7 +465,7 @@ int forward_graph(bk_engine *e, int T, int n_seq, int max_len) {
         cudaGraphExecDestroy(e->graphs[lru].exec);
         e->graphs.erase(e->graphs.begin() + (long)lru);
     }
-    e->graphs.push_back({T, n_seq, max_len, exec, e->graph_clock});
+    e->graphs.push_back({T, n_seq, max_len, slot, exec, e->graph_clock});
     CK(cudaGraphLaunch(exec, e->st));
     return 0;
 }
@@ -512,24 +524,38 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
     return 0;
 }
 
-BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq, float *out) {
+BK_API int bk_engine_submit(bk_engine *e, int32_t slot, const int32_t *tokens, const int32_t *lens, int32_t n_seq) {
     int T, mx;
+    if (slot < 0 || slot > 1) return fail("slot %d outside 0..1", slot);
     if (check_batch(e, lens, n_seq, &T, &mx)) return -1;
     CK(cudaSetDevice(e->device));
-    memcpy(e->h_tokens, tokens, (size_t)T * 4);
-    memcpy(e->h_lens, lens, (size_t)n_seq * 4);
-    CK(cudaMemcpyAsync(e->d_tokens, e->h_tokens, (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
-    CK(cudaMemcpyAsync(e->d_lens, e->h_lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
+    memcpy(e->h_tokens2[slot], tokens, (size_t)T * 4);
+    memcpy(e->h_lens2[slot], lens, (size_t)n_seq * 4);
+    CK(cudaMemcpyAsync(e->d_tokens2[slot], e->h_tokens2[slot], (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
+    CK(cudaMemcpyAsync(e->d_lens2[slot], e->h_lens2[slot], (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
     e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
     if (T <= e->graph_max_tokens && !e->keep_hidden && !e->timing) {
         // small batch: the 3 + 7*n_layer + 1 launches cost more host time than GPU time -> replay a captured graph
-        if (forward_graph(e, T, n_seq, mx)) return -1;
-    } else if (forward_device(e, e->d_tokens, e->d_lens, T, n_seq, mx, e->d_out)) return -1;
-    const size_t ob = (size_t)n_seq * e->hp.n_embd * 4;
-    CK(cudaMemcpyAsync(e->h_out, e->d_out, ob, cudaMemcpyDeviceToHost, e->st));
-    CK(cudaStreamSynchronize(e->st));
-    memcpy(out, e->h_out, ob);
+        if (forward_graph(e, slot, T, n_seq, mx)) return -1;
+    } else if (forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, e->d_out2[slot])) return -1;
+    CK(cudaMemcpyAsync(e->h_out2[slot], e->d_out2[slot], (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaEventRecord(e->slot_done[slot], e->st));
+    e->slot_nseq[slot] = n_seq;
     return 0;
+}
+
+BK_API int bk_engine_collect(bk_engine *e, int32_t slot, float *out) {
+    if (!e || slot < 0 || slot > 1 || e->slot_nseq[slot] <= 0) return fail("nothing submitted in slot %d", slot);
+    CK(cudaSetDevice(e->device));
+    CK(cudaEventSynchronize(e->slot_done[slot]));
+    memcpy(out, e->h_out2[slot], (size_t)e->slot_nseq[slot] * e->hp.n_embd * 4);
+    e->slot_nseq[slot] = 0;
+    return 0;
+}
+
+BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq, float *out) {
+    if (bk_engine_submit(e, 0, tokens, lens, n_seq)) return -1;
+    return bk_engine_collect(e, 0, out);
 }
 
 BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernels, float *ms_total) {

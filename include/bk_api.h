@@ -61,6 +61,13 @@ BK_API int bk_engine_finalize(bk_engine *e);
  * H2D copy, all kernels and the D2H copy run on the engine's stream; returns after it drained. */
 BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t *lens, int32_t n_seq, float *out);
 
+/* The same pass split in two so that consecutive batches overlap: submit stages the ids (pinned copy + H2D),
+ * enqueues all kernels and the D2H copy of the embeddings on the engine's stream and returns at once; collect
+ * waits for that batch and copies n_seq rows to `out`.  Two slots (0, 1): while the host collects and scatters
+ * slot s, the batch submitted to slot 1-s is already running. */
+BK_API int bk_engine_submit(bk_engine *e, int32_t slot, const int32_t *tokens, const int32_t *lens, int32_t n_seq);
+BK_API int bk_engine_collect(bk_engine *e, int32_t slot, float *out);
+
 /* Same work with the inputs already resident in HBM (bench.py `value` leg): stage a whole job once
  * (any number of sentences, in the caller's order; it is cut into micro-batches of <= cap_tokens /
  * cap_seqs), then run the kernels over all of it `iters` times, timed with CUDA events on the
