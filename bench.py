@@ -270,7 +270,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=os.environ.get("BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
-    ap.add_argument("--mb-tokens", type=int, default=int(os.environ.get("BERT_B200_MB_TOKENS", "32768")))
+    ap.add_argument("--mb-tokens", type=int, default=int(os.environ.get("BERT_B200_MB_TOKENS", "65536")))
     ap.add_argument("--vocab", type=int, default=30522)
     ap.add_argument("--ref-sentences", type=int, default=2, help="reference arm: sentences per step")
     ap.add_argument("--cpu-baseline-sentences", type=int, default=12)

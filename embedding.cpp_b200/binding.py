@@ -212,7 +212,7 @@ class Engine:
     """One-GPU engine through bk_api.h (bench.py's device-resident leg, hidden-state tests).  The GGUF
     file is parsed on the Python side (gguf_io.read_gguf) and handed over tensor by tensor."""
 
-    def __init__(self, gguf_path: str, device: int = 0, cap_tokens: int = 32768, cap_seqs: int = 8192, lib=None):
+    def __init__(self, gguf_path: str, device: int = 0, cap_tokens: int = 65536, cap_seqs: int = 8192, lib=None):
         self.lib = lib or load_library()
         g = _sibling("gguf_io")
         f = g.read_gguf(gguf_path)

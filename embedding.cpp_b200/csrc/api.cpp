@@ -131,7 +131,7 @@ BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
 
     const std::vector<int> devs = pick_devices();
     if (devs.empty()) { fprintf(stderr, "%s: no usable CUDA device (%s); this library has no CPU path\n", __func__, bk_last_error()); return nullptr; }
-    ctx->cap_tokens = env_int("BERT_B200_MB_TOKENS", 32768);
+    ctx->cap_tokens = env_int("BERT_B200_MB_TOKENS", 65536);
     if (ctx->cap_tokens < hp.n_max_tokens) ctx->cap_tokens = hp.n_max_tokens;
     ctx->cap_seqs = std::min(ctx->cap_tokens, env_int("BERT_B200_MB_SEQS", 8192));
     for (int dev : devs) {
