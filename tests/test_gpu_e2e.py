@@ -107,6 +107,20 @@ def test_q4_packed_weight_path_equals_f16_copy_path(ftype, binding, make_model, 
     assert np.array_equal(outs[0], outs[1])
 
 
+def test_many_short_sentences_cross_the_sequence_cap(binding, make_model):
+    """more sentences than one launch holds (cap_seqs = 8192): the batcher splits by sentence count, the on-device
+    scan runs several 1024-wide passes; every sentence must still equal its stand-alone evaluation"""
+    path = make_model("tiny", "f16", seed=46, n_vocab=300)
+    m = binding.BertB200(path)
+    rng = np.random.default_rng(14)
+    batch = [rand_tokens(rng, 300, int(L)) for L in rng.integers(1, 4, 9000)]
+    out = m.eval_batch(batch)
+    assert np.allclose(np.linalg.norm(out, axis=1), 1.0, atol=1e-3)
+    for i in (0, 1023, 1024, 8191, 8192, 8999):
+        assert np.array_equal(out[i], m.eval(batch[i]))
+    m.close()
+
+
 def test_multi_gpu_in_process_equals_single(binding, make_model, monkeypatch):
     """one bert_ctx spread over 2 GPUs (worker thread per GPU, host gather) returns what one GPU returns"""
     lib = binding.load_library()
