@@ -285,6 +285,25 @@ __device__ __forceinline__ float gelu_fast(float x) {
     return round_f16(__fmul_rn(__fmul_rn(0.5f, u), __fadd_rn(1.0f, t)));
 }
 
+// Two elements at a time with Blackwell's packed fp32 instructions (fma/add/mul.f32x2, sm_100+): each lane of
+// a packed op is the same IEEE operation as the scalar form above, so the results are bit-identical to
+// gelu_fast; the epilogue of the FFN-up GEMM is issue-slot bound and this halves its FP32 instruction count.
+// Returns the fp32 value BEFORE the final f16 rounding (the caller's f16 pack performs it once).
+__device__ __forceinline__ float2 gelu_fast2_unrounded(float2 x) {
+    const float2 u = __half22float2(__floats2half2_rn(x.x, x.y));
+    const float2 w = __ffma2_rn(make_float2(-0.1029432395800235f, -0.1029432395800235f), __fmul2_rn(u, u),
+                                make_float2(-2.302208198144325f, -2.302208198144325f));
+    const float2 z = __fmul2_rn(u, w);  // -2u*log2(e)
+    float2 e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(z.x));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(z.y));
+    const float2 d = __fadd2_rn(make_float2(1.0f, 1.0f), e);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.x) : "f"(d.x));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.y) : "f"(d.y));
+    const float2 t = __ffma2_rn(make_float2(2.0f, 2.0f), r, make_float2(-1.0f, -1.0f));  // tanh(u) rounded to fp32
+    return __fmul2_rn(__fmul2_rn(make_float2(0.5f, 0.5f), u), __fadd2_rn(make_float2(1.0f, 1.0f), t));
+}
+
 // Q8_0 / Q8_1 activation rounding of one 32-element block given its amax (quantize_row_q8_0 /
 // quantize_row_q8_1, AVX2 branches, ggml-quants.c:702-747, 944-985): d = amax/127 (Q8_0 stores it
 // as f16, Q8_1 keeps f32), q = rne(x * (127/amax)); the value the Q4 dot product then sees is d*q.
@@ -295,6 +314,15 @@ __device__ __forceinline__ void q8_scales(float amax, int mode, float &id, float
     dq = (mode == 1) ? round_f16(d) : d;
 }
 __device__ __forceinline__ float q8_round(float x, float id, float dq) { return dq * rintf(x * id); }
+// packed form: rne(x*id) via the 1.5*2^23 trick (exact for |x*id| <= 2^22; here <= 127), all on the FMA pipe
+__device__ __forceinline__ float2 q8_round2(float2 x, float id, float dq) {
+    const float2 magic = make_float2(12582912.f, 12582912.f);
+    // scalar products: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 (seen in SASS), which would skip the
+    // fp32 rounding of x*id that _mm256_mul_ps performs before _mm256_round_ps in the reference
+    const float2 m = make_float2(__fmul_rn(x.x, id), __fmul_rn(x.y, id));
+    const float2 q = __fadd2_rn(__fadd2_rn(m, magic), make_float2(-12582912.f, -12582912.f));
+    return __fmul2_rn(make_float2(dq, dq), q);
+}
 
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     __half2 h = __floats2half2_rn(a, b);

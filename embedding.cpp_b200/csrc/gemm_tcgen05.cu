@@ -329,47 +329,50 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 bph ^= 1u << b;
                 const int n = nb + half * 32;
                 if (n < p.N) {
+                    // all epilogue arithmetic on element PAIRS with the packed fp32 instructions (f32x2): the epilogue
+                    // warps are issue-slot bound, and each lane of a packed op is the scalar IEEE op
                     const float4 *b4 = reinterpret_cast<const float4 *>(p.bias + n);
-                    float v[32];
+                    float2 v[16];
 #pragma unroll
                     for (int j = 0; j < 8; j++) {
                         const float4 bb = __ldg(b4 + j);
-                        v[4 * j + 0] = __uint_as_float(acc[4 * j + 0]) + bb.x;
-                        v[4 * j + 1] = __uint_as_float(acc[4 * j + 1]) + bb.y;
-                        v[4 * j + 2] = __uint_as_float(acc[4 * j + 2]) + bb.z;
-                        v[4 * j + 3] = __uint_as_float(acc[4 * j + 3]) + bb.w;
+                        v[2 * j + 0] = __fadd2_rn(make_float2(__uint_as_float(acc[4 * j + 0]), __uint_as_float(acc[4 * j + 1])), make_float2(bb.x, bb.y));
+                        v[2 * j + 1] = __fadd2_rn(make_float2(__uint_as_float(acc[4 * j + 2]), __uint_as_float(acc[4 * j + 3])), make_float2(bb.z, bb.w));
                     }
                     if (has_resid) {
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
                             const uint4 u = *reinterpret_cast<const uint4 *>(box + row_off + ((((uint32_t)(half * 4 + j)) ^ sw) << 4));
-                            float2 f;
-                            f = unpack_h2(u.x); v[8 * j + 0] += f.x; v[8 * j + 1] += f.y;
-                            f = unpack_h2(u.y); v[8 * j + 2] += f.x; v[8 * j + 3] += f.y;
-                            f = unpack_h2(u.z); v[8 * j + 4] += f.x; v[8 * j + 5] += f.y;
-                            f = unpack_h2(u.w); v[8 * j + 6] += f.x; v[8 * j + 7] += f.y;
+                            v[4 * j + 0] = __fadd2_rn(v[4 * j + 0], unpack_h2(u.x));
+                            v[4 * j + 1] = __fadd2_rn(v[4 * j + 1], unpack_h2(u.y));
+                            v[4 * j + 2] = __fadd2_rn(v[4 * j + 2], unpack_h2(u.z));
+                            v[4 * j + 3] = __fadd2_rn(v[4 * j + 3], unpack_h2(u.w));
                         }
                     } else if (p.epi >= BK_EPI_BIAS_GELU) {
 #pragma unroll
-                        for (int j = 0; j < 32; j++) v[j] = gelu_fast(v[j]);
+                        for (int j = 0; j < 16; j++) v[j] = gelu_fast2_unrounded(v[j]);
                         if (p.epi != BK_EPI_BIAS_GELU) {
-                            // the next GEMM has Q4 weights: its input row is quantised per 32 (ggml.c:9493-9509)
+                            // the next GEMM has Q4 weights: its input row is quantised per 32 (ggml.c:9493-9509);
+                            // the quantiser sees the f16-rounded GELU value
                             float amax = 0.f;
 #pragma unroll
-                            for (int j = 0; j < 32; j++) amax = fmaxf(amax, fabsf(v[j]));
+                            for (int j = 0; j < 16; j++) {
+                                v[j] = unpack_h2(pack_h2(v[j].x, v[j].y));
+                                amax = fmaxf(amax, fmaxf(fabsf(v[j].x), fabsf(v[j].y)));
+                            }
                             float id, dq;
                             q8_scales(amax, p.epi == BK_EPI_BIAS_GELU_Q8_0 ? 1 : 2, id, dq);
 #pragma unroll
-                            for (int j = 0; j < 32; j++) v[j] = q8_round(v[j], id, dq);
+                            for (int j = 0; j < 16; j++) v[j] = q8_round2(v[j], id, dq);
                         }
                     }
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
                         uint4 u;
-                        u.x = pack_h2(v[8 * j + 0], v[8 * j + 1]);
-                        u.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
-                        u.z = pack_h2(v[8 * j + 4], v[8 * j + 5]);
-                        u.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
+                        u.x = pack_h2(v[4 * j + 0].x, v[4 * j + 0].y);
+                        u.y = pack_h2(v[4 * j + 1].x, v[4 * j + 1].y);
+                        u.z = pack_h2(v[4 * j + 2].x, v[4 * j + 2].y);
+                        u.w = pack_h2(v[4 * j + 3].x, v[4 * j + 3].y);
                         *reinterpret_cast<uint4 *>(box + row_off + ((((uint32_t)(half * 4 + j)) ^ sw) << 4)) = u;
                     }
                 }
@@ -562,7 +565,11 @@ cudaError_t launch_q4_retile(const void *src, int wtype, int n_rows, int K, void
 // ------------------------------------------------------------------------------ GELU alone (tests)
 __global__ void gelu_test_kernel(const float *__restrict__ x, float *__restrict__ y, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) y[i] = gelu_fast(x[i]);
+    if (i < n) {  // the packed form the GEMM epilogue uses (both lanes), checked against the scalar form
+        const float2 g = gelu_fast2_unrounded(make_float2(x[i], x[i]));
+        const float a = round_f16(g.x), b = round_f16(g.y);
+        y[i] = (a == b && a == gelu_fast(x[i])) ? a : __int_as_float(0x7fc00000);
+    }
 }
 cudaError_t launch_gelu_test(const float *x, float *y, int n, cudaStream_t st) {
     gelu_test_kernel<<<(n + 255) / 256, 256, 0, st>>>(x, y, n);
