@@ -7,7 +7,7 @@ NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-fvisibility=hidd
 CXXFLAGS  := -O2 -std=c++17 -fPIC -fvisibility=hidden -Wall -Wextra -Wno-unused-parameter -I/usr/local/cuda/include
 SRC       := embedding.cpp_b200/csrc
 OBJ       := build/obj
-CU_SRCS   := gemm_tcgen05.cu rowwise.cu attention_tc.cu engine.cu test_entry.cu
+CU_SRCS   := gemm_tcgen05.cu gemm_ln.cu rowwise.cu attention_tc.cu engine.cu test_entry.cu
 CPP_SRCS  := api.cpp gguf.cpp tokenizer_wp.cpp quantize.cpp
 OBJS      := $(addprefix $(OBJ)/,$(CU_SRCS:.cu=.o) $(CPP_SRCS:.cpp=.o))
 

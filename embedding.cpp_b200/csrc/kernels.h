@@ -43,6 +43,18 @@ bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_
 // y[i] = the epilogue's GELU of x[i] (tests)
 cudaError_t launch_gelu_test(const float *x, float *y, int n, cudaStream_t st);
 
+// ---- gemm_ln.cu -----------------------------------------------------------------------------
+// y = LN(A . W^T + bias + resid) * gamma + beta (and its Q8-rounded copy yq when qmode != 0) in one kernel:
+// clusters of CTA pairs hold whole 256 x N row blocks in TMEM.  N must be 384, 768 or 1024.
+// tmA: {K, M} box {64, 128}; tmRes / tmY / tmYQ: {N, M} box {64, 128}; all SWIZZLE_128B.
+bool gemm_ln_supported(int N, int K);
+cudaError_t launch_gemm_ln(const CUtensorMap &tmA, const WeightMaps &W, const CUtensorMap &tmRes, const CUtensorMap &tmY,
+                           const CUtensorMap *tmYQ, const float *bias, const float *gamma, const float *beta, float eps, int qmode,
+                           int M, int N, int K, int num_sms, cudaStream_t st);
+
+// tuning aid: 16 tiles x 8 clock64 stamps of block 0's first epilogue thread are written to dev_buf (null = off)
+void gemm_ln_set_trace(long long *dev_buf);
+
 // ---- rowwise.cu -----------------------------------------------------------------------------
 // cu_seqlens (exclusive prefix sum of lens, n_seq+1 entries) and per-token position inside its sentence
 cudaError_t launch_pack(const int32_t *lens, int n_seq, int32_t *cu_seqlens, int32_t *pos, int T, cudaStream_t st);

@@ -2,6 +2,7 @@
 // one kernel on the device, host buffers out.  Used by tests/ (parity per kernel against oracle/) and
 // for isolated ncu captures; the product path (engine.cu) launches the same kernels directly.
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -88,6 +89,69 @@ BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint1
     if (ms) *ms = t / reps;
     cudaEventDestroy(a); cudaEventDestroy(b);
     TCK(cudaMemcpy(out, dO.p, (size_t)M * N * 2, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+BK_API int bk_test_gemm_ln(int device, int32_t M, int32_t N, int32_t K, const uint16_t *A, const uint16_t *W, const float *bias,
+                           const uint16_t *resid, const float *gamma, const float *beta, float eps, int32_t qmode,
+                           uint16_t *y, uint16_t *yq, float *ms) {
+    TCK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    TCK(cudaGetDeviceProperties(&prop, device));
+    if (!gemm_ln_supported(N, K)) { fprintf(stderr, "bk_test_gemm_ln: unsupported N=%d K=%d\n", N, K); return -1; }
+    const size_t Mp = ((size_t)M + 255) / 256 * 256;  // whole cluster tiles: rows past M are written (finite garbage)
+    DevBuf dA, dW, dB, dG, dE, dR, dY, dQ;
+    TCK(dA.alloc(Mp * K * 2)); TCK(dW.alloc((size_t)N * K * 2)); TCK(dB.alloc((size_t)N * 4)); TCK(dG.alloc((size_t)N * 4));
+    TCK(dE.alloc((size_t)N * 4)); TCK(dR.alloc(Mp * N * 2)); TCK(dY.alloc(Mp * N * 2)); TCK(dQ.alloc(Mp * N * 2));
+    TCK(cudaMemset(dA.p, 0, Mp * K * 2)); TCK(cudaMemset(dR.p, 0, Mp * N * 2));
+    TCK(cudaMemcpy(dA.p, A, (size_t)M * K * 2, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dW.p, W, (size_t)N * K * 2, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dB.p, bias, (size_t)N * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dG.p, gamma, (size_t)N * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dE.p, beta, (size_t)N * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dR.p, resid, (size_t)M * N * 2, cudaMemcpyHostToDevice));
+    TCK(cudaMemset(dY.p, 0xFF, Mp * N * 2)); TCK(cudaMemset(dQ.p, 0xFF, Mp * N * 2));
+    CUtensorMap tmA, tmR, tmY, tmQ;
+    WeightMaps wm;
+    if (!make_tmap_f16_2d(&tmA, dA.p, K, Mp, (uint64_t)K * 2, GEMM_BLOCK_K, GEMM_BLOCK_M) || !make_weight_maps(&wm, dW.p, N, K) ||
+        !make_tmap_f16_2d(&tmR, dR.p, N, Mp, (uint64_t)N * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) ||
+        !make_tmap_f16_2d(&tmY, dY.p, N, Mp, (uint64_t)N * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) ||
+        !make_tmap_f16_2d(&tmQ, dQ.p, N, Mp, (uint64_t)N * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M)) {
+        fprintf(stderr, "bk_test_gemm_ln: cuTensorMapEncodeTiled failed\n");
+        return -1;
+    }
+    cudaEvent_t a, b;
+    TCK(cudaEventCreate(&a)); TCK(cudaEventCreate(&b));
+    const int reps = ms ? 5 : 1;
+    for (int w = 0; w < 2; w++) {  // w = 0: warm-up (first-use setup)
+        TCK(cudaEventRecord(a, 0));
+        for (int i = 0; i < (w ? reps : 1); i++)
+            TCK(launch_gemm_ln(tmA, wm, tmR, tmY, &tmQ, dB.as<float>(), dG.as<float>(), dE.as<float>(), eps, qmode, M, N, K,
+                               prop.multiProcessorCount, 0));
+        TCK(cudaEventRecord(b, 0));
+        TCK(cudaDeviceSynchronize());
+    }
+    float t = 0;
+    TCK(cudaEventElapsedTime(&t, a, b));
+    if (ms) *ms = t / reps;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    if (getenv("BERT_B200_LN_TRACE")) {  // phase durations (cycles) of the first tiles of block 0
+        DevBuf dT;
+        TCK(dT.alloc(16 * 8 * 8));
+        TCK(cudaMemset(dT.p, 0, 16 * 8 * 8));
+        gemm_ln_set_trace(dT.as<long long>());
+        TCK(launch_gemm_ln(tmA, wm, tmR, tmY, &tmQ, dB.as<float>(), dG.as<float>(), dE.as<float>(), eps, qmode, M, N, K, prop.multiProcessorCount, 0));
+        TCK(cudaDeviceSynchronize());
+        gemm_ln_set_trace(nullptr);
+        long long h[16 * 8];
+        TCK(cudaMemcpy(h, dT.p, sizeof h, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < 16 && h[i * 8]; i++)
+            fprintf(stderr, "tile %2d: wait_acc %6lld pass1 %6lld pass2 %6lld exch %6lld pass3 %6lld flush %6lld | tile %6lld\n", i, h[i * 8 + 1] - h[i * 8],
+                    h[i * 8 + 2] - h[i * 8 + 1], h[i * 8 + 3] - h[i * 8 + 2], h[i * 8 + 4] - h[i * 8 + 3], h[i * 8 + 5] - h[i * 8 + 4],
+                    h[i * 8 + 6] - h[i * 8 + 5], h[i * 8 + 6] - h[i * 8]);
+    }
+    TCK(cudaMemcpy(y, dY.p, (size_t)M * N * 2, cudaMemcpyDeviceToHost));
+    if (qmode && yq) TCK(cudaMemcpy(yq, dQ.p, (size_t)M * N * 2, cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -96,6 +96,12 @@ enum { BK_EPI_BIAS = 0, BK_EPI_BIAS_RESID = 1, BK_EPI_BIAS_GELU = 2, BK_EPI_BIAS
 BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint16_t *A, const void *W,
                         int32_t wtype, const float *bias, const uint16_t *resid, int32_t epi,
                         uint16_t *out, float *ms);
+/* the fused projection + residual + LayerNorm kernel (gemm_ln.cu): y = LN(A.W^T + bias + resid)*gamma + beta, f16 in /
+ * out, W f16 [N][K]; yq = the Q8-rounded copy when qmode 1=Q8_0 / 2=Q8_1.  N must be 384, 768 or 1024.
+ * Replaces ggml_mul_mat + add + add + ggml_norm + mul + add, bert.cpp:945-963 and 974-992. */
+BK_API int bk_test_gemm_ln(int device, int32_t M, int32_t N, int32_t K, const uint16_t *A, const uint16_t *W,
+                           const float *bias, const uint16_t *resid, const float *gamma, const float *beta, float eps,
+                           int32_t qmode, uint16_t *y, uint16_t *yq, float *ms);
 /* the GEMM epilogue's GELU alone: y[i] = f16(gelu(f16(x[i]))) -- ggml_vec_gelu_f32's f16 table, ggml.c:1418-1441 */
 BK_API int bk_test_gelu(int device, int32_t n, const float *x, float *y);
 /* LN(x)*gamma+beta over rows of `pre` (f16) -> y f16 (+ yq = Q8-rounded copy when qmode 1=Q8_0, 2=Q8_1);

@@ -181,6 +181,44 @@ def test_add_ln(lib, orc, make_model, T, d, qmode):
         assert (err <= step * 1.01 + 1e-3).all()
 
 
+@pytest.mark.parametrize("M,N,K", [(256, 768, 768), (1000, 768, 768), (37, 768, 3072), (5000, 384, 384), (300, 384, 1536),
+                                   (777, 1024, 1024), (256, 1024, 4096), (20000, 768, 768)])
+@pytest.mark.parametrize("qmode", [0, 1, 2])
+def test_gemm_ln_fused(lib, orc, make_model, M, N, K, qmode):
+    """projection + bias + residual + LayerNorm (+ Q8 rounding) in ONE kernel (gemm_ln.cu: clusters of CTA pairs hold
+    whole rows in TMEM, statistics exchanged through distributed shared memory) against fp32 NumPy + the oracle's
+    LayerNorm (ggml.c:8976-9004) and Q8 round trip (ggml-quants.c:702-747, 944-985)."""
+    if qmode and M > 5000:
+        pytest.skip("large case once")
+    rng = np.random.default_rng(M + N + K + qmode)
+    A = h(rng.standard_normal((M, K)) * 0.5)
+    W = h(rng.standard_normal((N, K)) * 0.05)
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float32)
+    resid = h(rng.standard_normal((M, N)) + 0.3)
+    gamma = (1 + 0.1 * rng.standard_normal(N)).astype(np.float32)
+    beta = (0.1 * rng.standard_normal(N)).astype(np.float32)
+    y = np.zeros((M, N), np.float16)
+    yq = np.zeros((M, N), np.float16)
+    assert lib.bk_test_gemm_ln(0, M, N, K, u16(A), u16(W), bias.ctypes.data_as(_f32p), u16(resid), gamma.ctypes.data_as(_f32p),
+                               beta.ctypes.data_as(_f32p), 1e-12, qmode, u16(y), u16(yq), None) == 0
+    pre = A.astype(np.float32) @ W.astype(np.float32).T + bias + resid.astype(np.float32)
+    o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+    o.hp.eps = 1e-12
+    ref = o.layernorm(np.ascontiguousarray(pre), gamma, beta)
+    err = np.abs(y.astype(np.float32) - ref)
+    assert (err <= 2e-3 * np.abs(ref) + 2e-3).all(), (float(err.max()), np.argwhere(err > 2e-3 * np.abs(ref) + 2e-3)[:5])
+    if qmode:
+        got = y.astype(np.float32)   # the kernel quantises its own fp32 LN value; compare against the round trip of y
+        want = np.zeros_like(got)
+        fn = o.lib.oracle_quant_q8_0_roundtrip if qmode == 1 else o.lib.oracle_quant_q8_1_roundtrip
+        fn(np.ascontiguousarray(ref).ctypes.data_as(_f32p), want.ctypes.data_as(_f32p), ref.size)
+        step = np.abs(ref).reshape(M, N // 32, 32).max(-1, keepdims=True) / 127.0
+        step = np.broadcast_to(step, (M, N // 32, 32)).reshape(M, N)
+        errq = np.abs(yq.astype(np.float32) - want)
+        assert (errq <= 1e-3 * np.abs(want) + 1e-5).mean() > 0.99   # fp32 GEMM-order differences can flip a .5 rounding
+        assert (errq <= step * 1.01 + 2e-3).all()
+
+
 @pytest.mark.parametrize("d,H,lens", [(128, 4, [5, 128, 1, 33]), (256, 4, [64, 17, 200]), (768, 12, [128, 128, 16]),
                                       (384, 12, [512, 2]), (256, 4, [512, 300, 129])])
 def test_attention(lib, orc, make_model, d, H, lens):
