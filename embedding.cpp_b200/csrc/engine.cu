@@ -98,6 +98,7 @@ struct bk_engine {
     CUtensorMap tm_x, tm_att, tm_y, tm_h;  // A-operand maps (x/y point at the Q8-rounded copy for Q4 models)
     CUtensorMap to_qkv, to_pre, to_h;      // GEMM output maps (TMA stores), box {64, 128}
     CUtensorMap tr_x, tr_y;                // residual maps (unrounded x / y), box {64, 128}
+    CUtensorMap to_xq, to_yq;              // Q4 models: the Q8-rounded copies as outputs of the fused GEMM + LayerNorm kernel
     CUtensorMap ta_qkv;                    // attention's view of qkv: box {dh, 64 rows}
     // pinned staging
     // staged batch
@@ -121,6 +122,10 @@ struct bk_engine {
     // only Q4 bytes cross HBM: weight traffic dominates there); larger ones use the f16 operand copies, where
     // weights are < 2% of the bytes moved and the decode would compete with the epilogue for issue slots.
     int q4_smem_tokens = 1024;    // BERT_B200_Q4_SMEM_TOKENS; -1 = always, 0 = never
+    // batches of more than this many tokens run attention-output and FFN-down as ONE kernel each with the residual add and
+    // the LayerNorm in the GEMM epilogue (gemm_ln.cu: a cluster per 256-row block); smaller ones have too few row blocks to
+    // fill the clusters and use GEMM(+bias+residual) followed by add_ln.  BERT_B200_FUSED_LN_TOKENS; -1 = never
+    int fused_ln_tokens = 4096;
     // timing
     std::vector<cudaEvent_t> ev;
     std::vector<int> ev_kind;
@@ -203,6 +208,7 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     e->qmode = hp->wtype == BK_Q4_0 ? 1 : hp->wtype == BK_Q4_1 ? 2 : 0;
     if (const char *v = getenv("BERT_B200_GRAPH_TOKENS")) e->graph_max_tokens = atoi(v);
     if (const char *v = getenv("BERT_B200_Q4_SMEM_TOKENS")) e->q4_smem_tokens = atoi(v);
+    if (const char *v = getenv("BERT_B200_FUSED_LN_TOKENS")) e->fused_ln_tokens = atoi(v);
     e->tens.resize(5 + 16 * (size_t)hp->n_layer);
     e->layers.resize(hp->n_layer);
     if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) { fail("cudaStreamCreate failed"); delete e; return nullptr; }
@@ -344,6 +350,8 @@ BK_API int bk_engine_finalize(bk_engine *e) {
               make_tmap_f16_2d(&e->to_h, e->h, f, T, f * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
               make_tmap_f16_2d(&e->tr_x, e->x, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
               make_tmap_f16_2d(&e->tr_y, e->y, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
+              (!e->qmode || (make_tmap_f16_2d(&e->to_xq, e->xq, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
+                             make_tmap_f16_2d(&e->to_yq, e->yq, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M))) &&
               make_tmap_attention(&e->ta_qkv, e->qkv, (int)d, hp.n_head, T);
     if (!ok) return fail("cuTensorMapEncodeTiled failed for activation buffers");
     e->finalized = true;
@@ -413,16 +421,25 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
             CK(launch_attention(e->ta_qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
             e->launch_count++;
         }
-        if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, L.po, T, d, d, L.bo, &e->tr_x, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
-        {
+        const bool fused_ln = e->fused_ln_tokens >= 0 && T > e->fused_ln_tokens && gemm_ln_supported(d, d) && gemm_ln_supported(d, f);
+        if (fused_ln) {  // y = LN(att.Wo^T + bo + x) in one kernel (tr_y doubles as the output map of y: same box geometry)
+            KTimer t(e, BK_K_GEMM_O);
+            CK(launch_gemm_ln(e->tm_att, L.tm_wo, e->tr_x, e->tr_y, q ? &e->to_yq : nullptr, L.bo, L.ln1g, L.ln1b, hp.eps, q, T, d, d, e->num_sms, e->st));
+            e->launch_count++;
+        } else {
+            if (run_gemm(e, BK_K_GEMM_O, e->tm_att, L.tm_wo, L.po, T, d, d, L.bo, &e->tr_x, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
             KTimer t(e, BK_K_ADD_LN);
             CK(launch_add_ln(e->pre, L.ln1g, L.ln1b, T, d, hp.eps, e->y, e->yq, q, e->st));
             e->launch_count++;
         }
         const int epi1 = q == 0 ? BK_EPI_BIAS_GELU : q == 1 ? BK_EPI_BIAS_GELU_Q8_0 : BK_EPI_BIAS_GELU_Q8_1;
         if (run_gemm(e, BK_K_GEMM_FF1, e->tm_y, L.tm_w1, L.p1, T, f, d, L.b1, nullptr, e->to_h, epi1)) return -1;
-        if (run_gemm(e, BK_K_GEMM_FF2, e->tm_h, L.tm_w2, L.p2, T, d, f, L.b2, &e->tr_y, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
-        {
+        if (fused_ln) {  // x = LN(h.W2^T + b2 + y)
+            KTimer t(e, BK_K_GEMM_FF2);
+            CK(launch_gemm_ln(e->tm_h, L.tm_w2, e->tr_y, e->tr_x, q ? &e->to_xq : nullptr, L.b2, L.ln2g, L.ln2b, hp.eps, q, T, d, f, e->num_sms, e->st));
+            e->launch_count++;
+        } else {
+            if (run_gemm(e, BK_K_GEMM_FF2, e->tm_h, L.tm_w2, L.p2, T, d, f, L.b2, &e->tr_y, e->to_pre, BK_EPI_BIAS_RESID)) return -1;
             KTimer t(e, BK_K_ADD_LN);
             CK(launch_add_ln(e->pre, L.ln2g, L.ln2b, T, d, hp.eps, e->x, e->xq, q, e->st));
             e->launch_count++;

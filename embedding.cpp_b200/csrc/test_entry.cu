@@ -146,9 +146,9 @@ BK_API int bk_test_gemm_ln(int device, int32_t M, int32_t N, int32_t K, const ui
         long long h[16 * 8];
         TCK(cudaMemcpy(h, dT.p, sizeof h, cudaMemcpyDeviceToHost));
         for (int i = 0; i < 16 && h[i * 8]; i++)
-            fprintf(stderr, "tile %2d: wait_acc %6lld pass1 %6lld pass2 %6lld exch %6lld pass3 %6lld flush %6lld | tile %6lld\n", i, h[i * 8 + 1] - h[i * 8],
+            fprintf(stderr, "tile %2d: wait_acc %6lld pass1 %6lld stats %6lld pass2 %6lld flush %6lld | tile %6lld\n", i, h[i * 8 + 1] - h[i * 8],
                     h[i * 8 + 2] - h[i * 8 + 1], h[i * 8 + 3] - h[i * 8 + 2], h[i * 8 + 4] - h[i * 8 + 3], h[i * 8 + 5] - h[i * 8 + 4],
-                    h[i * 8 + 6] - h[i * 8 + 5], h[i * 8 + 6] - h[i * 8]);
+                    h[i * 8 + 5] - h[i * 8]);
     }
     TCK(cudaMemcpy(y, dY.p, (size_t)M * N * 2, cudaMemcpyDeviceToHost));
     if (qmode && yq) TCK(cudaMemcpy(yq, dQ.p, (size_t)M * N * 2, cudaMemcpyDeviceToHost));

@@ -154,6 +154,7 @@ SHAPES = {  # name -> BertHParams overrides (BASELINE.json configs)
     "tiny": dict(n_embd=64, n_intermediate=128, n_head=2, n_layer=2, n_max_tokens=64),
     "mini": dict(n_embd=128, n_intermediate=512, n_head=4, n_layer=2, n_max_tokens=512),
     "mini64": dict(n_embd=256, n_intermediate=1024, n_head=4, n_layer=2, n_max_tokens=512),  # head size 64
+    "mini384": dict(n_embd=384, n_intermediate=768, n_head=6, n_layer=2, n_max_tokens=512),  # n_embd the fused GEMM+LN kernel takes
 }
 
 

@@ -107,6 +107,28 @@ def test_q4_packed_weight_path_equals_f16_copy_path(ftype, binding, make_model, 
     assert np.array_equal(outs[0], outs[1])
 
 
+@pytest.mark.parametrize("ftype", ["f16", "q4_0", "q4_1"])
+def test_fused_gemm_layernorm_path(ftype, binding, orc, make_model, monkeypatch):
+    """large batches run attention-output and FFN-down with the residual add and the LayerNorm inside the GEMM epilogue
+    (gemm_ln.cu); forced here for every batch size: same gate against the oracle, and the same embeddings (to fp32
+    rounding of the LayerNorm input, which the unfused path rounds to f16) as the GEMM + add_ln path"""
+    path = make_model("mini384", ftype, seed=47)
+    o = orc.Oracle(path)
+    rng = np.random.default_rng(19)
+    lens = [1, 2, 31, 128, 129, 300, 512] + list(rng.integers(1, 260, 40))   # > 4 cluster tiles of 256 rows
+    batch = [rand_tokens(rng, 500, int(L)) for L in lens]
+    outs = {}
+    for lim in ("0", "-1"):                              # always fused / never fused
+        monkeypatch.setenv("BERT_B200_FUSED_LN_TOKENS", lim)
+        m = binding.BertB200(path)
+        outs[lim] = m.eval_batch(batch)
+        m.close()
+    for t, g, u in zip(batch, outs["0"], outs["-1"]):
+        check(g, o.eval(t), ftype, f"fused mini384 {ftype} L={len(t)}")
+        c, mx = cos_maxabs(g, u)
+        assert c >= 0.99999 and (ftype.startswith("q4") or mx <= 5e-4), (len(t), c, mx)
+
+
 def test_many_short_sentences_cross_the_sequence_cap(binding, make_model):
     """more sentences than one launch holds (cap_seqs = 8192): the batcher splits by sentence count, the on-device
     scan runs several 1024-wide passes; every sentence must still equal its stand-alone evaluation"""
