@@ -312,42 +312,44 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             if (tracer) p.trace[iter * 8 + 3] = clock64();
             // ------------------------------------------ pass 2: normalise, gamma, beta, store
-            const float2 nmean = make_float2(-mean, -mean), rs2 = make_float2(rstd, rstd);
+            // y = ((x - mean) * rstd) * gamma + beta as two packed FMAs per element pair: x * rstd + (-mean * rstd), then
+            // * gamma + beta.  The reference rounds after each of its four nodes (ggml.c:8996-9004, bert.cpp:958-963); the
+            // fused form differs from that by at most an fp32 ulp, far below the f16 rounding of the stored result
+            const float2 rs2 = make_float2(rstd, rstd), sh2 = make_float2(-mean * rstd, -mean * rstd);
+            // Q4 models: sweep 0 stages y for every box of the team, sweep 1 re-reads x from TMEM, normalises again and
+            // stages the Q8-rounded copy in the same boxes -- by then the y store of the box has normally been read, so
+            // the team does not stall on it (keeping y in registers across the boxes would not fit in 96 registers)
+            const int n_sweep = p.qmode ? 2 : 1;
 #pragma unroll 1
-            for (int b = team; b < NBOX; b += 2) {
-                const int col = b * GEMM_OUT_BOX_N + half * 32;
-                uint8_t *box = obuf + b * kLnBoxBytes;
-                uint32_t acc[32];
-                tmem_ld_32x32(taddr + (uint32_t)col, acc);
-                tmem_ld_wait();
-                if (b + 2 >= NBOX) {  // last TMEM read of this stage by this warp: hand the accumulator back
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive_cluster(tempty_lead0 + 8u * as);
-                }
-                const float4 *g4 = reinterpret_cast<const float4 *>(p.gamma + ncol0 + col);
-                const float4 *e4 = reinterpret_cast<const float4 *>(p.beta + ncol0 + col);
-                float amax = 0.f;
+            for (int sweep = 0; sweep < n_sweep; sweep++) {
+#pragma unroll 1
+                for (int b = team; b < NBOX; b += 2) {
+                    const int col = b * GEMM_OUT_BOX_N + half * 32;
+                    uint8_t *box = obuf + b * kLnBoxBytes;
+                    uint32_t acc[32];
+                    tmem_ld_32x32(taddr + (uint32_t)col, acc);
+                    tmem_ld_wait();
+                    if (sweep == n_sweep - 1 && b + 2 >= NBOX) {  // last TMEM read of this stage by this warp: hand the accumulator back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(tempty_lead0 + 8u * as);
+                    }
+                    const float4 *g4 = reinterpret_cast<const float4 *>(p.gamma + ncol0 + col);
+                    const float4 *e4 = reinterpret_cast<const float4 *>(p.beta + ncol0 + col);
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const float4 g = __ldg(g4 + j), be = __ldg(e4 + j);
-                    float2 a = make_float2(__uint_as_float(acc[4 * j + 0]), __uint_as_float(acc[4 * j + 1]));
-                    float2 c = make_float2(__uint_as_float(acc[4 * j + 2]), __uint_as_float(acc[4 * j + 3]));
-                    a = __fmul2_rn(__fadd2_rn(a, nmean), rs2);
-                    c = __fmul2_rn(__fadd2_rn(c, nmean), rs2);
-                    // three roundings as the reference's norm, ggml_mul, ggml_add nodes (scalar products: ptxas would
-                    // contract a packed mul + add into FFMA2)
-                    a = __fadd2_rn(make_float2(__fmul_rn(g.x, a.x), __fmul_rn(g.y, a.y)), make_float2(be.x, be.y));
-                    c = __fadd2_rn(make_float2(__fmul_rn(g.z, c.x), __fmul_rn(g.w, c.y)), make_float2(be.z, be.w));
-                    acc[4 * j + 0] = __float_as_uint(a.x); acc[4 * j + 1] = __float_as_uint(a.y);
-                    acc[4 * j + 2] = __float_as_uint(c.x); acc[4 * j + 3] = __float_as_uint(c.y);
-                    amax = fmaxf(amax, fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(c.x), fabsf(c.y))));
-                }
-#pragma unroll 1
-                for (int pass = 0; pass < 2; pass++) {  // pass 0: y, pass 1: the Q8-rounded copy (Q4 models)
-                    if (pass == 1) {
-                        if (!p.qmode) break;
-                        ln_wait(&oread_bar[b], iter & 1, 9);  // the y store has finished reading the box
+                    for (int j = 0; j < 8; j++) {
+                        const float4 g = __ldg(g4 + j), be = __ldg(e4 + j);
+                        float2 a = make_float2(__uint_as_float(acc[4 * j + 0]), __uint_as_float(acc[4 * j + 1]));
+                        float2 c = make_float2(__uint_as_float(acc[4 * j + 2]), __uint_as_float(acc[4 * j + 3]));
+                        a = __ffma2_rn(__ffma2_rn(a, rs2, sh2), make_float2(g.x, g.y), make_float2(be.x, be.y));
+                        c = __ffma2_rn(__ffma2_rn(c, rs2, sh2), make_float2(g.z, g.w), make_float2(be.z, be.w));
+                        acc[4 * j + 0] = __float_as_uint(a.x); acc[4 * j + 1] = __float_as_uint(a.y);
+                        acc[4 * j + 2] = __float_as_uint(c.x); acc[4 * j + 3] = __float_as_uint(c.y);
+                    }
+                    if (sweep == 1) {
+                        float amax = 0.f;  // of the fp32 LayerNorm output, as quantize_row_q8_0/1 see it (ggml.c:9493-9509)
+#pragma unroll
+                        for (int j = 0; j < 16; j++) amax = fmaxf(amax, fmaxf(fabsf(__uint_as_float(acc[2 * j])), fabsf(__uint_as_float(acc[2 * j + 1]))));
                         float id, dq;
                         q8_scales(amax, p.qmode, id, dq);
 #pragma unroll
@@ -355,6 +357,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             const float2 v = q8_round2(make_float2(__uint_as_float(acc[2 * j]), __uint_as_float(acc[2 * j + 1])), id, dq);
                             acc[2 * j] = __float_as_uint(v.x); acc[2 * j + 1] = __float_as_uint(v.y);
                         }
+                        ln_wait(&oread_bar[b], iter & 1, 9);  // the y store has finished reading the box
                     }
                     // in place: this thread overwrites exactly the residual chunks it read in pass 1
 #pragma unroll
