@@ -212,21 +212,25 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                     for (int i = 0; i < 32; i++) if (i >= nv) a[i] = 0xff800000u;
                 }
                 uint32_t pk[16];
-                float s0 = 0.f, s1 = 0.f;
+                float2 s2 = make_float2(0.f, 0.f);
+                const float2 sc2 = make_float2(scale, scale), nmx2 = make_float2(-mx, -mx), l2e = make_float2(1.4426950408889634f, 1.4426950408889634f);
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
-                    // ggml_scale (separate multiply), x - max, f16 round | exp | f16 round   (ggml.c:10536-10558)
-                    const float x0 = __fsub_rn(__fmul_rn(__uint_as_float(a[i]), scale), mx);
-                    const float x1 = __fsub_rn(__fmul_rn(__uint_as_float(a[i + 1]), scale), mx);
-                    const float2 y = __half22float2(__floats2half2_rn(x0, x1));
+                    // ggml_scale (separate multiply), x - max, f16 round | exp | f16 round   (ggml.c:10536-10558), on element
+                    // pairs with the packed fp32 instructions (each lane is the scalar IEEE op; the product is formed with
+                    // scalar multiplies because ptxas contracts a packed mul + add into one FFMA2, which would skip the
+                    // reference's rounding of s*scale)
+                    const float2 x = __fadd2_rn(make_float2(__fmul_rn(__uint_as_float(a[i]), scale), __fmul_rn(__uint_as_float(a[i + 1]), scale)), nmx2);
+                    const float2 z = __fmul2_rn(__half22float2(__floats2half2_rn(x.x, x.y)), l2e);
                     float e0, e1;
-                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(y.x * 1.4426950408889634f));
-                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(y.y * 1.4426950408889634f));
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(z.x));
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(z.y));
                     const __half2 hp = __floats2half2_rn(e0, e1);
-                    const float2 f = __half22float2(hp);
-                    s0 += f.x; s1 += f.y;
+                    s2 = __fadd2_rn(s2, __half22float2(hp));
                     pk[i >> 1] = *reinterpret_cast<const uint32_t *>(&hp);
                 }
+                const float s0 = s2.x, s1 = s2.y;
+                (void)sc2;
                 sum += s0 + s1;
 #pragma unroll
                 for (int q = 0; q < 4; q++)
