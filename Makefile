@@ -11,7 +11,7 @@ CU_SRCS   := gemm_tcgen05.cu gemm_ln.cu rowwise.cu attention_tc.cu engine.cu tes
 CPP_SRCS  := api.cpp gguf.cpp tokenizer_wp.cpp quantize.cpp
 OBJS      := $(addprefix $(OBJ)/,$(CU_SRCS:.cu=.o) $(CPP_SRCS:.cpp=.o))
 
-all: build/libbert.so
+all: build/libbert.so build/bert-server
 
 build/libbert.so: $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -cudart static -lpthread -ldl -lrt
@@ -22,6 +22,10 @@ $(OBJ)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/kernels.h include/bk_api.h | $(
 
 $(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/gguf.h $(SRC)/tokenizer_wp.h include/bert.h include/bk_api.h | $(OBJ)
 	$(CXX) $(CXXFLAGS) -c $< -o $@
+
+# the reference's examples/server.cpp protocol with dynamic batching across connections
+build/bert-server: $(SRC)/server.cpp $(SRC)/server_batcher.h include/bert.h build/libbert.so
+	$(CXX) $(CXXFLAGS) -o $@ $(SRC)/server.cpp -Lbuild -lbert -Wl,-rpath,'$$ORIGIN' -lpthread
 
 $(OBJ):
 	mkdir -p $(OBJ)
