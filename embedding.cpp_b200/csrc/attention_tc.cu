@@ -61,40 +61,49 @@ __device__ __forceinline__ uint32_t att_idesc(uint32_t N, uint32_t b_mn) {
 
 template <int DH, int G>
 __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__restrict__ cu,
-                                                                    int d, __half *__restrict__ out, int qmode, float scale) {
+                                                                    int d, __half *__restrict__ out, int qmode, float scale, int multi) {
     constexpr int ROWB = DH * 2;           // bytes per smem row of Q / K / V
     constexpr int CW = 4 * G;              // control warp
     constexpr int NSOFT = 128 * G;         // softmax threads
     constexpr int PBUF = kAttQ * 128;      // one P chunk: 128 rows x 64 keys f16
-    extern __shared__ uint8_t att_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(att_raw) + 1023) & ~uintptr_t(1023));
+    extern __shared__ __align__(1024) uint8_t att_raw[];  // swizzle atoms need 1024-byte alignment; no static shared memory in this kernel
+    uint8_t *smem = att_raw;
 
-    const int seq = blockIdx.z, head = blockIdx.y, q0 = blockIdx.x * kAttQ;
+    const int seq = blockIdx.z, head = blockIdx.y;
     const int t0 = __ldg(cu + seq);
     const int L = __ldg(cu + seq + 1) - t0;
-    if (q0 >= L) return;
+    if (L <= 0) return;
+    const int nqb = (L + kAttQ - 1) / kAttQ;  // 128-query blocks of this sentence, processed one after the other by this CTA
     const int Lk16 = (L + 15) & ~15;       // keys entering the MMAs
     const int Lk64 = (L + 63) & ~63;       // keys staged in smem (whole 64-row TMA boxes)
     const int n_chunks = Lk64 >> 6;
     const int n_slices = (L + 31) >> 5;    // 32-key slices holding at least one real key
 
-    // region 0: Q | K while S is computed, then the two P chunk buffers; region 1: V
+    // multi == 0 (launches with max_len <= 128: one query block per sentence): region 0 = Q | K while S is computed, then
+    // the two P chunk buffers; region 1 = V.  48 KB for dh = 64, four CTAs per SM.
+    // multi == 1: K and V of the (sentence, head) stay resident for all its query blocks, Q is double buffered (block
+    // i+1 is fetched while block i is in the softmax) and P has buffers of its own: Q0 | Q1 | P0 | P1 | K | V.
     const int qk_bytes = (kAttQ + Lk64) * ROWB;
     const int r0_bytes = qk_bytes > 2 * PBUF ? qk_bytes : 2 * PBUF;
-    uint8_t *sQ = smem, *sK = smem + kAttQ * ROWB, *sP = smem, *sV = smem + r0_bytes;
+    uint8_t *sQ = smem;
+    uint8_t *sP = multi ? smem + 2 * kAttQ * ROWB : smem;
+    const uint32_t npb = multi ? 4u : 2u;  // P chunk buffers: with four, a softmax group never waits for the MMA of its own previous chunk
+    uint8_t *sK = multi ? sP + 4 * PBUF : smem + kAttQ * ROWB;
+    uint8_t *sV = multi ? sK + Lk64 * ROWB : smem + r0_bytes;
     uint8_t *tail = sV + Lk64 * ROWB;
-    uint64_t *bar_qk = reinterpret_cast<uint64_t *>(tail);
-    uint64_t *bar_v = bar_qk + 1, *bar_s = bar_qk + 2, *bar_o = bar_qk + 3, *pfull = bar_qk + 4, *pfree = bar_qk + 6;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_qk + 8);
-    float *red = reinterpret_cast<float *>(bar_qk + 10);  // [G][128] partial row max, then partial row sums
+    uint64_t *bar_q = reinterpret_cast<uint64_t *>(tail);  // [2] Q buffer landed
+    uint64_t *bar_k = bar_q + 2, *bar_v = bar_q + 3, *bar_s = bar_q + 4, *bar_o = bar_q + 5, *pfull = bar_q + 6, *pfree = bar_q + 10;
+    uint64_t *bar_tfree = bar_q + 14;                      // every softmax warp has read O: TMEM may take the next score block
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_q + 15);
+    float *red = reinterpret_cast<float *>(bar_q + 16);    // [G][128] partial row max, then partial row sums
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == CW) {
         if (lane == 0) {
             tma_prefetch_desc(&tmQKV);
-            mbar_init(bar_qk, 1); mbar_init(bar_v, 1); mbar_init(bar_s, 1); mbar_init(bar_o, 1);
-            mbar_init(&pfull[0], 4 * (G >= 2 ? 2 : 1)); mbar_init(&pfull[1], 4 * (G >= 2 ? 2 : 1));
-            mbar_init(&pfree[0], 1); mbar_init(&pfree[1], 1);
+            mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1); mbar_init(bar_k, 1); mbar_init(bar_v, 1); mbar_init(bar_s, 1); mbar_init(bar_o, 1);
+            mbar_init(bar_tfree, 4 * G);
+            for (int i = 0; i < 4; i++) { mbar_init(&pfull[i], 4 * (G >= 2 ? 2 : 1)); mbar_init(&pfree[i], 1); }
             mbar_fence_init();
         }
         __syncwarp();
@@ -114,43 +123,75 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
     if (warp == CW) {
         // ================================================================ control warp (uniform, elected issue)
         const int cq = head * DH, ck = d + head * DH, cv = 2 * d + head * DH;
-        mbar_expect_tx_e(bar_qk, (uint32_t)qk_bytes);
-        tma_load_2d_e(sQ, &tmQKV, bar_qk, cq, t0 + q0);
-        tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, bar_qk, cq, t0 + q0 + 64);
-        for (int c = 0; c < n_chunks; c++) tma_load_2d_e(sK + c * 64 * ROWB, &tmQKV, bar_qk, ck, t0 + c * 64);
+        mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
+        tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, t0);
+        tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, t0 + 64);
+        mbar_expect_tx_e(bar_k, (uint32_t)(Lk64 * ROWB));
+        for (int c = 0; c < n_chunks; c++) tma_load_2d_e(sK + c * 64 * ROWB, &tmQKV, bar_k, ck, t0 + c * 64);
         mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
         for (int c = 0; c < n_chunks; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
 
-        // ---- S = Q . K^T : N = Lk16 split into instructions of <= 256 columns
-        mbar_wait(bar_qk, 0);
-        tc_fence_after();
-        const uint64_t dq = umma_desc_kmajor<ROWB>(smem_u32(sQ));
-        for (int n0 = 0; n0 < Lk16; n0 += 256) {
-            const int nn = Lk16 - n0 < 256 ? Lk16 - n0 : 256;
-            const uint64_t dk = umma_desc_kmajor<ROWB>(smem_u32(sK + n0 * ROWB));
-            const uint32_t idesc = att_idesc((uint32_t)nn, 0);
-#pragma unroll
-            for (int k = 0; k < DH / 16; k++)
-                umma_f16_e<1>(tmem_base + (uint32_t)n0, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
-        }
-        umma_commit_e<1>(bar_s);
-
-        // ---- O += P_c . V_c as the softmax warps deliver P chunks
-        mbar_wait(bar_v, 0);
         const uint32_t idesc_pv = att_idesc(DH, 1);
-        for (int c = 0; c < n_chunks; c++) {
-            mbar_wait(&pfull[c & 1], (uint32_t)((c >> 1) & 1));
-            tc_fence_after();
-            const uint64_t dp = umma_desc_sw128(smem_u32(sP + (c & 1) * PBUF));
-            const int rem = Lk16 - c * 64;
-            const int ksteps = rem >= 64 ? 4 : rem >> 4;
-            for (int ks = 0; ks < ksteps; ks++) {
-                const uint64_t dv = umma_desc_mnmajor<ROWB>(smem_u32(sV + (c * 64 + ks * 16) * ROWB));
-                umma_f16_e<1>(tmem_base, dp + (uint64_t)(2 * ks), dv, idesc_pv, (c | ks) != 0);
+        // S = Q . K^T for key columns [n_lo, n_hi): instructions of <= 256 columns
+        auto issue_s = [&](int qb, int n_lo, int n_hi) {
+            const uint64_t dq = umma_desc_kmajor<ROWB>(smem_u32(sQ + (qb & 1) * kAttQ * ROWB));
+            for (int n0 = n_lo; n0 < n_hi; n0 += 256) {
+                const int nn = n_hi - n0 < 256 ? n_hi - n0 : 256;
+                const uint64_t dk = umma_desc_kmajor<ROWB>(smem_u32(sK + n0 * ROWB));
+                const uint32_t idesc = att_idesc((uint32_t)nn, 0);
+#pragma unroll
+                for (int k = 0; k < DH / 16; k++)
+                    umma_f16_e<1>(tmem_base + (uint32_t)n0, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
             }
-            umma_commit_e<1>(&pfree[c & 1]);
+        };
+        const int n_split = Lk16 < DH ? Lk16 : DH;  // score columns [0, n_split) are the ones O aliases
+        mbar_wait(&bar_q[0], 0);
+        mbar_wait(bar_k, 0);
+        tc_fence_after();
+        issue_s(0, 0, Lk16);
+        umma_commit_e<1>(bar_s);
+        if (nqb > 1) {  // fetch the second query block while the first is computed
+            uint8_t *qn = sQ + kAttQ * ROWB;
+            mbar_expect_tx_e(&bar_q[1], (uint32_t)(kAttQ * ROWB));
+            tma_load_2d_e(qn, &tmQKV, &bar_q[1], cq, t0 + kAttQ);
+            tma_load_2d_e(qn + 64 * ROWB, &tmQKV, &bar_q[1], cq, t0 + kAttQ + 64);
         }
-        umma_commit_e<1>(bar_o);
+        mbar_wait(bar_v, 0);
+        uint32_t cg = 0;  // P chunks issued so far over all query blocks (buffer = cg % npb)
+        for (int qb = 0; qb < nqb; qb++) {
+            // ---- O += P_c . V_c as the softmax warps deliver P chunks
+            for (int c = 0; c < n_chunks; c++, cg++) {
+                const uint32_t pbi = cg % npb;
+                mbar_wait(&pfull[pbi], (cg / npb) & 1);
+                tc_fence_after();
+                const uint64_t dp = umma_desc_sw128(smem_u32(sP + pbi * PBUF));
+                const int rem = Lk16 - c * 64;
+                const int ksteps = rem >= 64 ? 4 : rem >> 4;
+                for (int ks = 0; ks < ksteps; ks++) {
+                    const uint64_t dv = umma_desc_mnmajor<ROWB>(smem_u32(sV + (c * 64 + ks * 16) * ROWB));
+                    umma_f16_e<1>(tmem_base, dp + (uint64_t)(2 * ks), dv, idesc_pv, (c | ks) != 0);
+                }
+                umma_commit_e<1>(&pfree[pbi]);
+            }
+            umma_commit_e<1>(bar_o);
+            if (qb + 1 < nqb) {
+                // every P chunk of this block has been delivered, so every softmax read of its scores is over: the
+                // next block's scores can already go to the columns O does not alias, behind the P.V MMAs in the pipe
+                mbar_wait(&bar_q[(qb + 1) & 1], (uint32_t)(((qb + 1) >> 1) & 1));
+                tc_fence_after();
+                issue_s(qb + 1, n_split, Lk16);
+                if (qb + 2 < nqb) {  // Q buffer of block qb is free (its S MMAs retired long ago): fetch block qb+2
+                    uint8_t *qn = sQ + (qb & 1) * kAttQ * ROWB;
+                    mbar_expect_tx_e(&bar_q[qb & 1], (uint32_t)(kAttQ * ROWB));
+                    tma_load_2d_e(qn, &tmQKV, &bar_q[qb & 1], cq, t0 + (qb + 2) * kAttQ);
+                    tma_load_2d_e(qn + 64 * ROWB, &tmQKV, &bar_q[qb & 1], cq, t0 + (qb + 2) * kAttQ + 64);
+                }
+                mbar_wait(bar_tfree, (uint32_t)(qb & 1));  // the softmax warps have read O: columns [0, dh) are free too
+                tc_fence_after();
+                issue_s(qb + 1, 0, n_split);
+                umma_commit_e<1>(bar_s);
+            }
+        }
     } else {
         // ======================================================================= softmax warps
         const int quad = warp & 3, g = warp >> 2;
@@ -160,7 +201,9 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
         // slice j (32 keys) -> chunk j/2, half j%2; owner group: G=1: 0, G=2: half, G=4: 2*(chunk%2) + half
         auto owner = [](int j) { return G == 1 ? 0 : G == 2 ? (j & 1) : (((j >> 1) & 1) << 1) | (j & 1); };
 
-        mbar_wait(bar_s, 0);
+        for (int qb = 0; qb < nqb; qb++) {
+        const int q0 = qb * kAttQ;
+        mbar_wait(bar_s, (uint32_t)(qb & 1));
         tc_fence_after();
         // ---- pass 1: row maximum of the raw scores over the real keys
         float mx = -INFINITY;
@@ -194,10 +237,12 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
         // ---- pass 2: p = f16(exp(f16(s*scale - max))) -> P chunk buffers
         float sum = 0.f;
         for (int c = 0; c < n_chunks; c++) {
-            // groups working on chunk c: G=1: {0}; G=2: {0,1}; G=4: {2*(c%2), 2*(c%2)+1}
-            if (G == 4 && (g >> 1) != (c & 1)) continue;
-            if (c >= 2) mbar_wait(&pfree[c & 1], (uint32_t)(((c >> 1) - 1) & 1));  // the MMAs that read this buffer retired
-            uint8_t *pb = sP + (c & 1) * PBUF;
+            const uint32_t cg = (uint32_t)(qb * n_chunks + c);  // chunk number over all query blocks: buffer cg & 1
+            // groups working on chunk cg: G=1: {0}; G=2: {0,1}; G=4: {2*(cg%2), 2*(cg%2)+1}
+            if (G == 4 && (uint32_t)(g >> 1) != (cg & 1)) continue;
+            const uint32_t pbi = cg % npb;
+            if (cg >= npb) mbar_wait(&pfree[pbi], ((cg / npb) - 1) & 1);  // the MMAs that read this buffer retired
+            uint8_t *pb = sP + pbi * PBUF;
 #pragma unroll 1
             for (int h = 0; h < 2; h++) {
                 if (G >= 2 && h != (g & 1)) continue;
@@ -220,17 +265,23 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                     // pairs with the packed fp32 instructions (each lane is the scalar IEEE op; the product is formed with
                     // scalar multiplies because ptxas contracts a packed mul + add into one FFMA2, which would skip the
                     // reference's rounding of s*scale)
-                    const float2 x = __fadd2_rn(make_float2(__fmul_rn(__uint_as_float(a[i]), scale), __fmul_rn(__uint_as_float(a[i + 1]), scale)), nmx2);
+                    float2 x;
+                    if (DH == 64)  // scale = 1/8: s*scale is exact, so one FMA gives fl(fl(s*scale) - max) bit for bit
+                        x = __ffma2_rn(make_float2(__uint_as_float(a[i]), __uint_as_float(a[i + 1])), sc2, nmx2);
+                    else
+                        x = __fadd2_rn(make_float2(__fmul_rn(__uint_as_float(a[i]), scale), __fmul_rn(__uint_as_float(a[i + 1]), scale)), nmx2);
                     const float2 z = __fmul2_rn(__half22float2(__floats2half2_rn(x.x, x.y)), l2e);
-                    float e0, e1;
-                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(z.x));
-                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(z.y));
-                    const __half2 hp = __floats2half2_rn(e0, e1);
+                    float2 e;
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(z.x));
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(z.y));
+                    const __half2 hp = __floats2half2_rn(e.x, e.y);
+                    // the row sum takes the f16-ROUNDED p (as the reference does): with 11-bit addends the fp32 partial sums
+                    // are exact for all practical rows, so the result does not depend on how keys are split over the softmax
+                    // groups (G = 1/2/4 by the launch's longest sentence): a sentence's embedding is batch-invariant
                     s2 = __fadd2_rn(s2, __half22float2(hp));
                     pk[i >> 1] = *reinterpret_cast<const uint32_t *>(&hp);
                 }
                 const float s0 = s2.x, s1 = s2.y;
-                (void)sc2;
                 sum += s0 + s1;
 #pragma unroll
                 for (int q = 0; q < 4; q++)
@@ -240,7 +291,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
             fence_proxy_async_smem();  // P writes -> visible to the MMA (async proxy)
             tc_fence_before();         // my TMEM reads of these score columns precede the MMA that may overwrite them (O aliases chunk 0)
             __syncwarp();
-            if (lane == 0) mbar_arrive(&pfull[c & 1]);
+            if (lane == 0) mbar_arrive(&pfull[pbi]);
         }
         if (G > 1) {
             red[g * 128 + r] = sum;
@@ -252,7 +303,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
         const float inv = 1.0f / sum;
 
         // ---- epilogue: O * inv, 32 features per (thread, pass)
-        mbar_wait(bar_o, 0);
+        mbar_wait(bar_o, (uint32_t)(qb & 1));
         tc_fence_after();
         for (int hc = g; hc < DH / 32; hc += G) {
             uint32_t a[32];
@@ -278,6 +329,11 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                                         pack_h2(o[8 * q + 4], o[8 * q + 5]), pack_h2(o[8 * q + 6], o[8 * q + 7]));
             }
         }
+        if (G > 1) named_bar_sync(1, NSOFT);  // every thread has read the row sums: red may take the next block's maxima
+        tc_fence_before();                    // my TMEM reads (S, O) precede the next block's S MMAs
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_tfree);
+        }  // query blocks
     }
 
     tc_fence_before();
@@ -298,7 +354,10 @@ static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_se
                               int qmode, cudaStream_t st) {
     const int Lk64 = (max_len + 63) & ~63;
     const int qk = (kAttQ + Lk64) * DH * 2;
-    const size_t smem = (size_t)(qk > 2 * kAttQ * 128 ? qk : 2 * kAttQ * 128) + (size_t)Lk64 * DH * 2 + 1024 /*align*/ + 128 + (size_t)G * 128 * 4;
+    const int multi = max_len > kAttQ ? 1 : 0;  // sentences span several 128-query blocks: one CTA per (sentence, head) keeps K, V resident
+    const size_t body = multi ? (size_t)2 * kAttQ * DH * 2 + 4 * kAttQ * 128 + (size_t)2 * Lk64 * DH * 2
+                              : (size_t)(qk > 2 * kAttQ * 128 ? qk : 2 * kAttQ * 128) + (size_t)Lk64 * DH * 2;
+    const size_t smem = body + 256 /*barriers*/ + (size_t)G * 128 * 4;
     static bool attr_set[64] = {false};  // per kernel instance and device (the attribute is per device)
     int dev = 0;
     cudaGetDevice(&dev);
@@ -307,9 +366,9 @@ static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_se
         if (err != cudaSuccess) return err;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    dim3 grid((max_len + kAttQ - 1) / kAttQ, n_head, n_seq);
+    dim3 grid(1, n_head, n_seq);
     const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934: 1.0f/sqrt((float)dh) evaluated in double
-    attention_tc_kernel<DH, G><<<grid, 32 + 128 * G, smem, st>>>(tm, cu, d, out, qmode, scale);
+    attention_tc_kernel<DH, G><<<grid, 32 + 128 * G, smem, st>>>(tm, cu, d, out, qmode, scale, multi);
     return cudaGetLastError();
 }
 
