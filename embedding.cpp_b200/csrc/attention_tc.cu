@@ -12,6 +12,7 @@
 //            written as the f16 A operand of the second MMA, 64 keys per chunk, double buffered
 //   tcgen05  O += P_chunk . V_chunk  (V consumed MN-major straight from its [key][dh] layout), O in TMEM
 //            columns [0, dh) which alias the already-consumed first score columns
+//   tcgen05  rowsum += P_chunk . 1  (an all-ones 16-column B tile): sum p lands in TMEM next to O
 //   epilogue O * (1 / sum p)  [+ Q8 rounding per 32 features for Q4 models, ggml.c:9493-9509] -> f16 rows
 //
 // Because the full score row is resident in TMEM, the true row maximum is known before any exponential
@@ -59,6 +60,24 @@ __device__ __forceinline__ uint32_t att_idesc(uint32_t N, uint32_t b_mn) {
     return (1u << 4) | (b_mn << 16) | ((N >> 3) << 17) | ((128u >> 4) << 24);
 }
 
+// one TMEM column: lane i of the warp reads TMEM lane (taddr.lane + i)
+__device__ __forceinline__ uint32_t tmem_ld_32x1(uint32_t taddr) {
+    uint32_t v;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v) : "r"(taddr) : "memory");
+    return v;
+}
+// K-major operand without swizzle, used only for the all-ones tile of the row-sum MMA: every byte the MMA can
+// address from it (LBO / SBO inside the 512-byte tile) is the same f16 1.0, so the core-matrix order is immaterial
+__device__ __forceinline__ uint64_t umma_desc_ones(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)(128 >> 4) << 16;
+    d |= (uint64_t)(256 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+constexpr int kSumCols = 16;  // TMEM columns [dh, dh + 16) take the row sums (every one of the 16 holds the same value)
+
 template <int DH, int G>
 __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__restrict__ cu,
                                                                     int d, __half *__restrict__ out, int qmode, float scale, int multi) {
@@ -95,7 +114,8 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
     uint64_t *bar_k = bar_q + 2, *bar_v = bar_q + 3, *bar_s = bar_q + 4, *bar_o = bar_q + 5, *pfull = bar_q + 6, *pfree = bar_q + 10;
     uint64_t *bar_tfree = bar_q + 14;                      // every softmax warp has read O: TMEM may take the next score block
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_q + 15);
-    float *red = reinterpret_cast<float *>(bar_q + 16);    // [G][128] partial row max, then partial row sums
+    float *red = reinterpret_cast<float *>(bar_q + 16);    // [G][128] partial row max
+    uint32_t *ones = reinterpret_cast<uint32_t *>(red + G * 128);  // 16 x 16 f16 1.0: B operand of the row-sum MMA (512 B)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == CW) {
@@ -106,9 +126,11 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
             for (int i = 0; i < 4; i++) { mbar_init(&pfull[i], 4 * (G >= 2 ? 2 : 1)); mbar_init(&pfree[i], 1); }
             mbar_fence_init();
         }
+        for (int i = lane; i < 128; i += 32) ones[i] = 0x3C003C00u;
+        fence_proxy_async_smem();
         __syncwarp();
-        // S needs Lk16 columns; O (dh columns) aliases columns [0, dh).  Power of two >= 32.
-        const int need = Lk16 > DH ? Lk16 : DH;
+        // S needs Lk16 columns; O (dh columns) and the row sums alias columns [0, dh + 16).  Power of two >= 32.
+        const int need = Lk16 > DH + kSumCols ? Lk16 : DH + kSumCols;
         if (need <= 32) tmem_alloc<32>(tmem_slot);
         else if (need <= 64) tmem_alloc<64>(tmem_slot);
         else if (need <= 128) tmem_alloc<128>(tmem_slot);
@@ -144,7 +166,12 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                     umma_f16_e<1>(tmem_base + (uint32_t)n0, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
             }
         };
-        const int n_split = Lk16 < DH ? Lk16 : DH;  // score columns [0, n_split) are the ones O aliases
+        const int n_split = Lk16 < DH + kSumCols ? Lk16 : DH + kSumCols;  // score columns [0, n_split) are the ones O and the row sums alias
+        const uint32_t idesc_sum = att_idesc(kSumCols, 0);
+        const uint64_t done = umma_desc_ones(smem_u32(ones));
+        // the row sums land in the score columns of chunk kLag, so the row-sum MMAs of chunk c are issued after chunk
+        // c + kLag has been consumed by the softmax warps (its P delivered)
+        constexpr int kLag = DH / 64;
         mbar_wait(&bar_q[0], 0);
         mbar_wait(bar_k, 0);
         tc_fence_after();
@@ -159,7 +186,16 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
         mbar_wait(bar_v, 0);
         uint32_t cg = 0;  // P chunks issued so far over all query blocks (buffer = cg % npb)
         for (int qb = 0; qb < nqb; qb++) {
-            // ---- O += P_c . V_c as the softmax warps deliver P chunks
+            // ---- O += P_c . V_c and rowsum += P_c . 1 as the softmax warps deliver P chunks
+            auto issue_sum = [&](int c, uint32_t cgc) {  // row sums of chunk c (global number cgc), then its P buffer is free
+                const uint32_t pbi = cgc % npb;
+                const uint64_t dp = umma_desc_sw128(smem_u32(sP + pbi * PBUF));
+                const int rem = Lk16 - c * 64;
+                const int ksteps = rem >= 64 ? 4 : rem >> 4;
+                for (int ks = 0; ks < ksteps; ks++)
+                    umma_f16_e<1>(tmem_base + (uint32_t)DH, dp + (uint64_t)(2 * ks), done, idesc_sum, (c | ks) != 0);
+                umma_commit_e<1>(&pfree[pbi]);
+            };
             for (int c = 0; c < n_chunks; c++, cg++) {
                 const uint32_t pbi = cg % npb;
                 mbar_wait(&pfull[pbi], (cg / npb) & 1);
@@ -171,8 +207,9 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                     const uint64_t dv = umma_desc_mnmajor<ROWB>(smem_u32(sV + (c * 64 + ks * 16) * ROWB));
                     umma_f16_e<1>(tmem_base, dp + (uint64_t)(2 * ks), dv, idesc_pv, (c | ks) != 0);
                 }
-                umma_commit_e<1>(&pfree[pbi]);
+                if (c >= kLag) issue_sum(c - kLag, cg - kLag);
             }
+            for (int c = n_chunks > kLag ? n_chunks - kLag : 0; c < n_chunks; c++) issue_sum(c, cg - (uint32_t)(n_chunks - c));
             umma_commit_e<1>(bar_o);
             if (qb + 1 < nqb) {
                 // every P chunk of this block has been delivered, so every softmax read of its scores is over: the
@@ -230,12 +267,11 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
             named_bar_sync(1, NSOFT);
 #pragma unroll
             for (int gg = 0; gg < G; gg++) mx = fmaxf(mx, red[gg * 128 + r]);
-            named_bar_sync(1, NSOFT);  // red is reused for the sums
+            // (red is next written for the following query block, after every warp has passed bar_tfree / bar_s)
         }
         mx *= scale;  // max(s*scale) == max(s)*scale for scale > 0 (rounding is monotonic)
 
         // ---- pass 2: p = f16(exp(f16(s*scale - max))) -> P chunk buffers
-        float sum = 0.f;
         for (int c = 0; c < n_chunks; c++) {
             const uint32_t cg = (uint32_t)(qb * n_chunks + c);  // chunk number over all query blocks: buffer cg & 1
             // groups working on chunk cg: G=1: {0}; G=2: {0,1}; G=4: {2*(cg%2), 2*(cg%2)+1}
@@ -257,7 +293,6 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                     for (int i = 0; i < 32; i++) if (i >= nv) a[i] = 0xff800000u;
                 }
                 uint32_t pk[16];
-                float2 s2 = make_float2(0.f, 0.f);
                 const float2 sc2 = make_float2(scale, scale), nmx2 = make_float2(-mx, -mx), l2e = make_float2(1.4426950408889634f, 1.4426950408889634f);
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
@@ -275,14 +310,8 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(z.x));
                     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(z.y));
                     const __half2 hp = __floats2half2_rn(e.x, e.y);
-                    // the row sum takes the f16-ROUNDED p (as the reference does): with 11-bit addends the fp32 partial sums
-                    // are exact for all practical rows, so the result does not depend on how keys are split over the softmax
-                    // groups (G = 1/2/4 by the launch's longest sentence): a sentence's embedding is batch-invariant
-                    s2 = __fadd2_rn(s2, __half22float2(hp));
                     pk[i >> 1] = *reinterpret_cast<const uint32_t *>(&hp);
                 }
-                const float s0 = s2.x, s1 = s2.y;
-                sum += s0 + s1;
 #pragma unroll
                 for (int q = 0; q < 4; q++)
                     *reinterpret_cast<uint4 *>(pb + row_off + ((((uint32_t)(h * 4 + q)) ^ sw) << 4)) =
@@ -293,22 +322,29 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
             __syncwarp();
             if (lane == 0) mbar_arrive(&pfull[pbi]);
         }
-        if (G > 1) {
-            red[g * 128 + r] = sum;
-            named_bar_sync(1, NSOFT);
-            sum = 0.f;
-#pragma unroll
-            for (int gg = 0; gg < G; gg++) sum += red[gg * 128 + r];
-        }
-        const float inv = 1.0f / sum;
-
-        // ---- epilogue: O * inv, 32 features per (thread, pass)
+        // ---- epilogue: O * (1 / sum p), 32 features per (thread, pass).  The row sum comes out of the tensor core too:
+        // rowsum = P . 1 accumulated next to O (TMEM column dh), i.e. the sum of the f16-rounded p over ALL keys in fp32,
+        // in one fixed key order whatever the number of softmax groups -- a sentence's result does not depend on the batch
+        // it is in -- and without the f16 -> f32 widening + add per element that the issue-bound softmax loop had
         mbar_wait(bar_o, (uint32_t)(qb & 1));
         tc_fence_after();
+        const float sum = __uint_as_float(tmem_ld_32x1(taddr + (uint32_t)DH));
+        tmem_ld_wait();
+        const float inv = 1.0f / sum;
+        if (g >= DH / 32) {  // this group reads no O columns: its part of TMEM is free for the next query block right away
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tfree);
+        }
         for (int hc = g; hc < DH / 32; hc += G) {
             uint32_t a[32];
             tmem_ld_32x32(taddr + (uint32_t)(hc * 32), a);
             tmem_ld_wait();
+            if (hc + G >= DH / 32) {  // last TMEM read of this block by this warp: the next block's last score columns may be
+                tc_fence_before();    // issued while the scaling / rounding / stores below run
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_tfree);
+            }
             float o[32];
 #pragma unroll
             for (int i = 0; i < 32; i++) o[i] = __uint_as_float(a[i]) * inv;
@@ -329,10 +365,6 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
                                         pack_h2(o[8 * q + 4], o[8 * q + 5]), pack_h2(o[8 * q + 6], o[8 * q + 7]));
             }
         }
-        if (G > 1) named_bar_sync(1, NSOFT);  // every thread has read the row sums: red may take the next block's maxima
-        tc_fence_before();                    // my TMEM reads (S, O) precede the next block's S MMAs
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_tfree);
         }  // query blocks
     }
 
@@ -340,7 +372,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
     __syncthreads();
     if (warp == CW) {
         tc_fence_after();
-        const int need = Lk16 > DH ? Lk16 : DH;
+        const int need = Lk16 > DH + kSumCols ? Lk16 : DH + kSumCols;
         if (need <= 32) tmem_dealloc<32>(tmem_base);
         else if (need <= 64) tmem_dealloc<64>(tmem_base);
         else if (need <= 128) tmem_dealloc<128>(tmem_base);
@@ -357,7 +389,7 @@ static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_se
     const int multi = max_len > kAttQ ? 1 : 0;  // sentences span several 128-query blocks: one CTA per (sentence, head) keeps K, V resident
     const size_t body = multi ? (size_t)2 * kAttQ * DH * 2 + 4 * kAttQ * 128 + (size_t)2 * Lk64 * DH * 2
                               : (size_t)(qk > 2 * kAttQ * 128 ? qk : 2 * kAttQ * 128) + (size_t)Lk64 * DH * 2;
-    const size_t smem = body + 256 /*barriers*/ + (size_t)G * 128 * 4;
+    const size_t smem = body + 256 /*barriers*/ + (size_t)G * 128 * 4 + 512 /*ones tile*/;
     static bool attr_set[64] = {false};  // per kernel instance and device (the attribute is per device)
     int dev = 0;
     cudaGetDevice(&dev);
