@@ -32,7 +32,8 @@ struct bert_ctx {
     int32_t cls_id = -1, sep_id = -1, pad_id = -1, unk_id = 0;  // defaults bert.cpp:119-124
     WordPieceTokenizer tok;
     bool tok_ok = false;
-    std::vector<bk_engine *> engines;
+    std::vector<bk_engine *> engines;  // n_gpus distinct devices, engines.size() / n_gpus engines on each
+    int n_gpus = 1;
     int cap_tokens = 0, cap_seqs = 0;
     std::mutex mu;  // one in-flight call per context (the reference is not re-entrant either, bert.cpp:1056-1062)
 };
@@ -56,6 +57,19 @@ std::vector<std::string> tensor_names(int n_layer) {
     for (int l = 0; l < n_layer; l++)
         for (int k = 0; k < 16; k++) n.push_back("encoder.layer." + std::to_string(l) + "." + per[k]);
     return n;
+}
+
+// BERT_B200_ENGINES_PER_GPU (default 2) engines per listed GPU, each with its own stream and activation buffers: two
+// micro-batches of a job are then in flight per GPU, so the copies of one overlap the kernels of the other and the
+// SMs a kernel leaves empty (cluster placement, last wave) run the other micro-batch.  Order g0 g1 .. g0 g1 ..: the
+// first workers of a small job land on distinct GPUs.
+std::vector<int> replicate_devices(const std::vector<int> &devs) {
+    int per = env_int("BERT_B200_ENGINES_PER_GPU", 2);
+    if (per < 1) per = 1;
+    if (per > 4) per = 4;
+    std::vector<int> out;
+    for (int r = 0; r < per; r++) out.insert(out.end(), devs.begin(), devs.end());
+    return out;
 }
 
 std::vector<int> pick_devices() {
@@ -129,7 +143,9 @@ BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
     }
     hp.wtype = (int32_t)(std::max_element(cnt, cnt + 4) - cnt);
 
-    const std::vector<int> devs = pick_devices();
+    const std::vector<int> gpus = pick_devices();
+    const std::vector<int> devs = replicate_devices(gpus);
+    ctx->n_gpus = std::max<int>(1, (int)gpus.size());
     if (devs.empty()) { fprintf(stderr, "%s: no usable CUDA device (%s); this library has no CPU path\n", __func__, bk_last_error()); return nullptr; }
     ctx->cap_tokens = env_int("BERT_B200_MB_TOKENS", 65536);
     if (ctx->cap_tokens < hp.n_max_tokens) ctx->cap_tokens = hp.n_max_tokens;
@@ -149,8 +165,8 @@ BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
         if (bk_engine_finalize(e) != 0) { fprintf(stderr, "%s: %s\n", __func__, bk_last_error()); bert_free(ctx.release()); return nullptr; }
     }
     if (env_int("BERT_B200_VERBOSE", 0))
-        fprintf(stderr, "%s: %s: d=%d f=%d heads=%d layers=%d vocab=%d wtype=%d on %zu GPU(s), micro-batch %d tokens\n", __func__, fname,
-                hp.n_embd, hp.n_intermediate, hp.n_head, hp.n_layer, hp.n_vocab, hp.wtype, ctx->engines.size(), ctx->cap_tokens);
+        fprintf(stderr, "%s: %s: d=%d f=%d heads=%d layers=%d vocab=%d wtype=%d on %d GPU(s), %zu engine(s), micro-batch %d tokens\n", __func__, fname,
+                hp.n_embd, hp.n_intermediate, hp.n_head, hp.n_layer, hp.n_vocab, hp.wtype, ctx->n_gpus, ctx->engines.size(), ctx->cap_tokens);
     return ctx.release();
 }
 
@@ -186,7 +202,8 @@ BERT_API void bert_eval_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n
     for (int b = 0; b < n_batch_size; b++) total += n_tokens[b];
     const int n_eng = (int)ctx->engines.size();
     long long budget = ctx->cap_tokens;
-    if (n_eng > 1) budget = std::min<long long>(budget, std::max<long long>((total + n_eng - 1) / n_eng, N));
+    // several GPUs: one share per GPU (a GPU's second engine only takes work when its share exceeds a micro-batch)
+    if (ctx->n_gpus > 1) budget = std::min<long long>(budget, std::max<long long>((total + ctx->n_gpus - 1) / ctx->n_gpus, N));
     std::vector<MicroBatch> mbs;
     for (int i = 0; i < n_batch_size;) {
         int j = i, t = 0;
