@@ -381,6 +381,8 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
     }
 }
 
+#include "attention_persist.cuh"
+
 template <int DH, int G>
 static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_seq, int max_len, int d, int n_head, __half *out,
                               int qmode, cudaStream_t st) {
@@ -412,6 +414,16 @@ cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens
     static const int env_g = [] { const char *v = getenv("BERT_B200_ATT_G"); return v ? atoi(v) : 0; }();
     int G = max_len <= 128 ? 1 : max_len <= 256 ? 2 : 4;
     if (env_g == 1 || env_g == 2 || env_g == 4) G = env_g;
+    // launches of short sentences (<= BERT_B200_ATT_PERSIST tokens, default 48; 0 = never, 128 = whenever possible): persistent
+    // CTAs with two items in flight.  One CTA per item spends most of its life on set-up and load latency when a sentence
+    // is a few rows of a 128-row tile (measured on 65 536 tokens: 16-token sentences 379 -> 342 us, 32: 200 -> 174 us); from
+    // 64 tokens on, four independent CTAs per SM hide that better than two persistent ones (64: 122 vs 129 us, 128: 103 vs 119 us)
+    const char *pv = getenv("BERT_B200_ATT_PERSIST");  // read per launch: the tests switch it inside one process
+    const int persist_max = pv ? atoi(pv) : 48;
+    if (max_len <= kAttQ && max_len <= persist_max && env_g == 0) {
+        if (dh == 64) return launch_att_persist<64>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
+        if (dh == 32) return launch_att_persist<32>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
+    }
 #define BK_ATT(DH_)                                                                                      \
     switch (G) {                                                                                         \
         case 1: return launch_att<DH_, 1>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st); \

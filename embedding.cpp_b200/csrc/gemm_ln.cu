@@ -57,7 +57,11 @@ struct GemmLnCfg {
     static constexpr int B_BYTES = B_ROWS * GEMM_BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int NBOX = BNL / GEMM_OUT_BOX_N;            // 64-column boxes per CTA (3 or 4)
-    static constexpr int OUT_BYTES = NBOX * kLnBoxBytes;         // residual in, y / yq out, in place
+    // residual in, y / yq out, in place -- in a ring of NBOX + 1 physical boxes: use u = tile * NBOX + b of a box lives in
+    // physical box u % NRING, so the residual of (tile + 1, b) only waits for the store of (tile, b - 1), not (tile, b), and
+    // is already there when pass 1 of the next tile reaches it
+    static constexpr int NRING = NBOX + 1;
+    static constexpr int OUT_BYTES = NRING * kLnBoxBytes;
     static constexpr int PART_BYTES = 4 * GEMM_BLOCK_M * 8;      // (mean, M2) of the 4 column groups
     static constexpr int COMB_BYTES = GEMM_BLOCK_M * 8;          // this CTA's combined (mean, M2) per row
     static constexpr int RCV_BYTES = 2 * NPAIRS * GEMM_BLOCK_M * 8;  // [tile parity][sender pair][row]
@@ -67,7 +71,7 @@ struct GemmLnCfg {
     static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES;
     static_assert(STAGES >= 3, "operand ring too shallow");
-    static_assert((2 * STAGES + 4 + 4 * NBOX + 2) * 8 + 8 <= BAR_BYTES, "barrier area");
+    static_assert((2 * STAGES + 4 + 4 * NRING + 2) * 8 + 8 <= BAR_BYTES, "barrier area");
     static_assert(B_BYTES % 1024 == 0, "W tile ends on a swizzle atom");
 };
 
@@ -87,6 +91,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     using Cfg = GemmLnCfg<NPAIRS, BNL>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int NBOX = Cfg::NBOX;
+    constexpr int NRING = Cfg::NRING;
     constexpr int CSIZE = 2 * NPAIRS;  // CTAs per cluster
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -99,11 +104,11 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t *empty_bar = full_bar + STAGES;
     uint64_t *tfull_bar = empty_bar + STAGES;    // [2] accumulator stage complete
     uint64_t *tempty_bar = tfull_bar + 2;        // [2] accumulator stage drained (the leader CTA's is waited on)
-    uint64_t *rfull_bar = tempty_bar + 2;        // [NBOX] residual box landed
-    uint64_t *rfree_bar = rfull_bar + NBOX;      // [NBOX] the box's last store has read it: next residual may land
-    uint64_t *ofull_bar = rfree_bar + NBOX;      // [NBOX] output staged in the box by the 8 warps of its team
-    uint64_t *oread_bar = ofull_bar + NBOX;      // [NBOX] the y store has read the box: the team may stage yq (Q4 models)
-    uint64_t *stat_bar = oread_bar + NBOX;       // [2] (by tile parity) row statistics of all pairs present
+    uint64_t *rfull_bar = tempty_bar + 2;        // [NRING] (per physical box) residual landed
+    uint64_t *rfree_bar = rfull_bar + NRING;     // [NRING] the box's last store has read it: next residual may land
+    uint64_t *ofull_bar = rfree_bar + NRING;     // [NRING] output staged in the box by the 8 warps of its team
+    uint64_t *oread_bar = ofull_bar + NRING;     // [NRING] the y store has read the box: the team may stage yq (Q4 models)
+    uint64_t *stat_bar = oread_bar + NRING;      // [2] (by tile parity) row statistics of all pairs present
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(stat_bar + 2);
 
     const int warp = threadIdx.x >> 5;
@@ -125,7 +130,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (p.qmode) tma_prefetch_desc(&tmYQ);
         for (int i = 0; i < STAGES; i++) { mbar_init(&full_bar[i], 2); mbar_init(&empty_bar[i], 1); }
         for (int i = 0; i < 2; i++) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 2 * 16); mbar_init(&stat_bar[i], GEMM_BLOCK_M); }
-        for (int i = 0; i < NBOX; i++) { mbar_init(&rfull_bar[i], 1); mbar_init(&rfree_bar[i], 1); mbar_init(&ofull_bar[i], 8); mbar_init(&oread_bar[i], 1); }
+        for (int i = 0; i < NRING; i++) { mbar_init(&rfull_bar[i], 1); mbar_init(&rfree_bar[i], 1); mbar_init(&ofull_bar[i], 8); mbar_init(&oread_bar[i], 1); }
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc<512, 2>(tmem_slot);
@@ -180,28 +185,29 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int t = cluster_id; t < m_tiles; t += n_clusters, iter++) {
             const int m0 = t * 2 * GEMM_BLOCK_M + rank * GEMM_BLOCK_M;
             for (int b = 0; b < NBOX; b++) {
-                if (iter > 0) ln_wait(&rfree_bar[b], (iter - 1) & 1, 4);  // the previous tile's stores of this box have read it
-                mbar_expect_tx_e(&rfull_bar[b], kLnBoxBytes);
-                tma_load_2d_e(obuf + b * kLnBoxBytes, &tmRes, &rfull_bar[b], ncol0 + b * GEMM_OUT_BOX_N, m0);
+                const uint32_t u = iter * NBOX + b, pb = u % NRING, k = u / NRING;  // k-th use of physical box pb
+                if (k > 0) ln_wait(&rfree_bar[pb], (k - 1) & 1, 4);  // the stores of its previous use have read it
+                mbar_expect_tx_e(&rfull_bar[pb], kLnBoxBytes);
+                tma_load_2d_e(obuf + pb * kLnBoxBytes, &tmRes, &rfull_bar[pb], ncol0 + b * GEMM_OUT_BOX_N, m0);
             }
         }
     } else if (warp == 3) {
         // ================================================================= TMA-store issuer
         // a warp of its own, so that waiting for a store to finish reading its box (which releases the box to the
         // residual loader, or to the team for the yq copy) never stalls an epilogue warp
-        uint32_t oph = 0;  // bit b = parity of the next staging of box b
-        const int n_pass = p.qmode ? 2 : 1;
-        for (int t = cluster_id; t < m_tiles; t += n_clusters) {
+        const uint32_t n_pass = p.qmode ? 2 : 1;
+        uint32_t iter = 0;
+        for (int t = cluster_id; t < m_tiles; t += n_clusters, iter++) {
             const int m0 = t * 2 * GEMM_BLOCK_M + rank * GEMM_BLOCK_M;
-            for (int pass = 0; pass < n_pass; pass++)
+            for (uint32_t pass = 0; pass < n_pass; pass++)
                 for (int b = 0; b < NBOX; b++) {
-                    ln_wait(&ofull_bar[b], (oph >> b) & 1, 10);
-                    oph ^= 1u << b;
+                    const uint32_t u = iter * NBOX + b, pb = u % NRING, k = u / NRING;
+                    ln_wait(&ofull_bar[pb], (k * n_pass + pass) & 1, 10);  // a box is staged n_pass times per use
                     if (lane == 0) {
-                        tma_store_2d(pass == 0 ? &tmY : &tmYQ, obuf + b * kLnBoxBytes, ncol0 + b * GEMM_OUT_BOX_N, m0);
+                        tma_store_2d(pass == 0 ? &tmY : &tmYQ, obuf + pb * kLnBoxBytes, ncol0 + b * GEMM_OUT_BOX_N, m0);
                         bulk_commit_group();
                         bulk_wait_group_read<0>();
-                        mbar_arrive(pass == n_pass - 1 ? &rfree_bar[b] : &oread_bar[b]);
+                        mbar_arrive(pass == n_pass - 1 ? &rfree_bar[pb] : &oread_bar[pb]);
                     }
                     __syncwarp();
                 }
@@ -236,10 +242,11 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll 1
             for (int b = team; b < NBOX; b += 2) {
                 const int col = b * GEMM_OUT_BOX_N + half * 32;  // CTA-local column == TMEM column of the stage
-                const uint8_t *box = obuf + b * kLnBoxBytes;
+                const uint32_t u = iter * NBOX + b, pb = u % NRING, k = u / NRING;
+                const uint8_t *box = obuf + pb * kLnBoxBytes;
                 uint32_t acc[32];
                 tmem_ld_32x32(taddr + (uint32_t)col, acc);
-                ln_wait(&rfull_bar[b], iter & 1, 6);
+                ln_wait(&rfull_bar[pb], k & 1, 6);
                 tmem_ld_wait();
                 const float4 *b4 = reinterpret_cast<const float4 *>(p.bias + ncol0 + col);
 #pragma unroll
@@ -325,7 +332,8 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll 1
                 for (int b = team; b < NBOX; b += 2) {
                     const int col = b * GEMM_OUT_BOX_N + half * 32;
-                    uint8_t *box = obuf + b * kLnBoxBytes;
+                    const uint32_t u = iter * NBOX + b, pb = u % NRING, k = u / NRING;
+                    uint8_t *box = obuf + pb * kLnBoxBytes;
                     uint32_t acc[32];
                     tmem_ld_32x32(taddr + (uint32_t)col, acc);
                     tmem_ld_wait();
@@ -357,7 +365,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             const float2 v = q8_round2(make_float2(__uint_as_float(acc[2 * j]), __uint_as_float(acc[2 * j + 1])), id, dq);
                             acc[2 * j] = __float_as_uint(v.x); acc[2 * j + 1] = __float_as_uint(v.y);
                         }
-                        ln_wait(&oread_bar[b], iter & 1, 9);  // the y store has finished reading the box
+                        ln_wait(&oread_bar[pb], k & 1, 9);  // the y store has finished reading the box
                     }
                     // in place: this thread overwrites exactly the residual chunks it read in pass 1
 #pragma unroll
@@ -371,7 +379,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     }
                     fence_proxy_async_smem();  // my generic-proxy writes -> visible to the TMA store
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&ofull_bar[b]);
+                    if (lane == 0) mbar_arrive(&ofull_bar[pb]);
                 }
             }
             if (tracer) { p.trace[iter * 8 + 4] = clock64(); p.trace[iter * 8 + 5] = p.trace[iter * 8 + 4]; }

@@ -238,6 +238,36 @@ def test_attention(lib, orc, make_model, d, H, lens):
         off += n
 
 
+@pytest.mark.parametrize("d,H,n_seq,qmode", [(768, 12, 90, 0), (384, 12, 100, 0), (768, 12, 61, 1), (128, 2, 700, 2)])
+def test_attention_persistent_kernel(lib, orc, make_model, monkeypatch, d, H, n_seq, qmode):
+    """launches whose longest sentence has <= 128 tokens run persistent CTAs that walk over several (sentence, head)
+    items with two of them in flight (attention_persist.cuh): more items than CTAs, every key-chunk / slice boundary,
+    against the oracle and bit for bit against the one-CTA-per-item kernel"""
+    rng = np.random.default_rng(d + n_seq)
+    lens = [1, 15, 16, 17, 32, 33, 63, 64, 65, 96, 97, 127, 128] + [int(v) for v in rng.integers(1, 129, n_seq - 13)]
+    lens = [lens[i] for i in rng.permutation(len(lens))]
+    T = sum(lens)
+    qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
+    L = np.array(lens, np.int32)
+    outs = []
+    for persist in ("128", "0"):
+        monkeypatch.setenv("BERT_B200_ATT_PERSIST", persist)
+        out = np.zeros((T, d), np.float16)
+        assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(out)) == 0
+        outs.append(out)
+    assert np.array_equal(outs[0].view(np.uint16), outs[1].view(np.uint16))
+    if qmode == 0:
+        o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+        off = 0
+        for i, n in enumerate(lens):
+            if i < 40 or n in (1, 16, 17, 64, 65, 128):
+                blk = qkv[off:off + n].astype(np.float32)
+                ref = o.attention(blk[:, :d], blk[:, d:2 * d], blk[:, 2 * d:], H)
+                got = outs[0][off:off + n].astype(np.float32)
+                assert np.allclose(got, ref, rtol=2e-3, atol=2e-3), (i, n, float(np.abs(got - ref).max()))
+            off += n
+
+
 @pytest.mark.parametrize("d,lens", [(64, [1, 2, 64]), (384, [128, 7]), (768, [128] * 5 + [512]), (1024, [33])])
 def test_pool_norm(lib, orc, make_model, d, lens):
     rng = np.random.default_rng(d)
