@@ -382,6 +382,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
 }
 
 #include "attention_persist.cuh"
+#include "attention_stream.cuh"
 
 template <int DH, int G>
 static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_seq, int max_len, int d, int n_head, __half *out,
@@ -423,6 +424,13 @@ cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens
     if (max_len <= kAttQ && max_len <= persist_max && env_g == 0) {
         if (dh == 64) return launch_att_persist<64>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
         if (dh == 32) return launch_att_persist<32>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
+    }
+    // launches with sentences of more than 128 tokens: scores streamed through a TMEM ring (BERT_B200_ATT_STREAM=0: whole
+    // score block resident, attention_tc_kernel)
+    const char *sv = getenv("BERT_B200_ATT_STREAM");
+    if (max_len > kAttQ && (!sv || atoi(sv) != 0) && env_g == 0) {
+        if (dh == 64) return launch_att_stream<64>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
+        if (dh == 32) return launch_att_stream<32>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
     }
 #define BK_ATT(DH_)                                                                                      \
     switch (G) {                                                                                         \

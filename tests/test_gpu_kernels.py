@@ -268,6 +268,34 @@ def test_attention_persistent_kernel(lib, orc, make_model, monkeypatch, d, H, n_
             off += n
 
 
+@pytest.mark.parametrize("d,H,qmode", [(768, 12, 0), (384, 12, 0), (256, 4, 1), (128, 4, 2)])
+def test_attention_streaming_kernel(lib, orc, make_model, monkeypatch, d, H, qmode):
+    """launches with sentences of more than 128 tokens stream the scores through a two-slot TMEM ring and compute them
+    twice (attention_stream.cuh): every chunk / query-block boundary, short sentences inside a long launch, against the
+    oracle and bit for bit against the kernel that keeps the whole score block resident"""
+    rng = np.random.default_rng(d + qmode)
+    lens = [512, 511, 385, 384, 383, 300, 257, 256, 255, 200, 129, 128, 127, 100, 64, 33, 17, 16, 5, 1] + [int(v) for v in rng.integers(1, 513, 12)]
+    T = sum(lens)
+    qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
+    L = np.array(lens, np.int32)
+    outs = []
+    for stream in ("1", "0"):
+        monkeypatch.setenv("BERT_B200_ATT_STREAM", stream)
+        out = np.zeros((T, d), np.float16)
+        assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(out)) == 0
+        outs.append(out)
+    assert np.array_equal(outs[0].view(np.uint16), outs[1].view(np.uint16))
+    if qmode == 0:
+        o = orc.Oracle(make_model("tiny", "f32", 13, 300))
+        off = 0
+        for i, n in enumerate(lens):
+            blk = qkv[off:off + n].astype(np.float32)
+            ref = o.attention(blk[:, :d], blk[:, d:2 * d], blk[:, 2 * d:], H)
+            got = outs[0][off:off + n].astype(np.float32)
+            assert np.allclose(got, ref, rtol=2e-3, atol=2e-3), (i, n, float(np.abs(got - ref).max()))
+            off += n
+
+
 @pytest.mark.parametrize("d,lens", [(64, [1, 2, 64]), (384, [128, 7]), (768, [128] * 5 + [512]), (1024, [33])])
 def test_pool_norm(lib, orc, make_model, d, lens):
     rng = np.random.default_rng(d)
