@@ -31,9 +31,9 @@ constexpr int kStreamKeys = 128;          // keys per score chunk
 constexpr int kStreamRing = 3;            // score slots in TMEM
 constexpr int kStreamQ = 2;               // Q buffers
 
-// shared memory behind Q | P | K | V: barriers + TMEM slot (160 B), all-ones tile (512 B), then one or two row-maximum
+// shared memory behind Q | P | K | V: barriers + TMEM slot (192 B), all-ones tile (512 B), then one or two row-maximum
 // exchange buffers of 2 KB
-constexpr int kStreamTail = 160 + 512;
+constexpr int kStreamTail = 192 + 512;
 
 template <int DH>
 __global__ void __launch_bounds__(kStreamThreads, 1)
@@ -61,14 +61,15 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
     uint8_t *sV = sK + Lk64 * ROWB;
     uint8_t *tail = sV + Lk64 * ROWB;
     uint64_t *bar_q = reinterpret_cast<uint64_t *>(tail);  // [2] Q buffer landed
-    uint64_t *bar_k = bar_q + 2, *bar_v = bar_q + 3;
+    uint64_t *bar_k = bar_q + 20;   // [4] keys [128 c, 128 c + 128) landed: the first score chunk does not wait for all of K
+    uint64_t *bar_v = bar_q + 3;
     uint64_t *sfull = bar_q + 4;    // [3] score chunk complete in the ring slot
     uint64_t *sfree = bar_q + 7;    // [3] all 16 warps have read the slot
     uint64_t *pfull = bar_q + 10;   // [2 pairs][2 slots] P slot written by the 8 warps of its group pair
     uint64_t *pfree = bar_q + 14;   // [2 pairs][2 slots] the MMAs that read the P slot have retired
     uint64_t *bar_o = bar_q + 18;   // O and row sums of a query block complete
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_q + 19);
-    uint32_t *ones = reinterpret_cast<uint32_t *>(bar_q + 20);  // 512 B, 16 x 16 f16 1.0
+    uint32_t *ones = reinterpret_cast<uint32_t *>(bar_q + 24);  // 512 B, 16 x 16 f16 1.0
     // [1 or 2][4][128] partial row maxima.  Two buffers (by block parity) when this sentence has <= 2 chunks per pass: a
     // warp ahead of the others could otherwise publish the next block's maximum while a slow one still reads this
     // block's.  With >= 3 chunks a group pair cannot get more than two P slots ahead of the other pair (the control warp
@@ -80,7 +81,8 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
     if (warp == CW) {
         if (lane == 0) {
             tma_prefetch_desc(&tmQKV);
-            mbar_init(bar_k, 1); mbar_init(bar_v, 1); mbar_init(bar_o, 1);
+            for (int i = 0; i < 4; i++) mbar_init(&bar_k[i], 1);
+            mbar_init(bar_v, 1); mbar_init(bar_o, 1);
             mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
             for (int i = 0; i < 3; i++) { mbar_init(&sfull[i], 1); mbar_init(&sfree[i], 16); }
             for (int i = 0; i < 4; i++) { mbar_init(&pfull[i], 8); mbar_init(&pfree[i], 1); }
@@ -108,8 +110,11 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
             tma_load_2d_e(q + 64 * ROWB, &tmQKV, bar, cq, t0 + qb * kAttQ + 64);
         };
         load_q(0);
-        mbar_expect_tx_e(bar_k, (uint32_t)(Lk64 * ROWB));
-        for (int c = 0; c < n_box; c++) tma_load_2d_e(sK + c * 64 * ROWB, &tmQKV, bar_k, ck, t0 + c * 64);
+        for (int c = 0; c < nc; c++) {  // K in chunks of 128 keys (two 64-row boxes, the last chunk possibly one)
+            const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
+            mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
+            for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, t0 + (2 * c + b) * 64);
+        }
         if (nqb > 1) load_q(1);
         mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
         for (int c = 0; c < n_box; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
@@ -122,8 +127,8 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
         int jq = 0, jc = 0;               // B jobs: block jq, chunk jc; A jobs: block jq + 1 (block 0 in the prologue), chunk jc
         const uint64_t dk0 = umma_desc_kmajor<ROWB>(smem_u32(sK));
         const uint64_t dq0 = umma_desc_kmajor<ROWB>(smem_u32(sQ));
-        mbar_wait(bar_k, 0);
         for (int js = 0; js < n_jobs; js++) {
+            if (js < nc) mbar_wait(&bar_k[js], 0);  // prologue job A(0, js): the first user of key chunk js
             if (js >= kStreamRing) mbar_wait(&sfree[slot], sph ^ 1);  // the slot has been read by all softmax warps (three jobs ago)
             const int blk = job_a ? (prologue ? 0 : jq + 1) : jq;
             if (job_a && jc == 0) {
