@@ -48,7 +48,7 @@ constexpr int kLnEpiWarp0 = 4;
 constexpr int kLnSmemLimit = 227 * 1024;
 constexpr int kLnBoxBytes = GEMM_BLOCK_M * GEMM_OUT_BOX_N * 2;  // 16 KB
 
-template <int NPAIRS, int BNL>
+template <int NPAIRS, int BNL, int YQ>
 struct GemmLnCfg {
     static_assert(BNL == 192 || BNL == 256, "columns per CTA pair = one UMMA N");
     static_assert(NPAIRS >= 2 && NPAIRS <= 4, "cluster of 4, 6 or 8 CTAs");
@@ -62,16 +62,20 @@ struct GemmLnCfg {
     // is already there when pass 1 of the next tile reaches it
     static constexpr int NRING = NBOX + 1;
     static constexpr int OUT_BYTES = NRING * kLnBoxBytes;
+    // YQ = 1 (Q4 models, short K): the Q8-rounded copy gets a staging box per epilogue team, so y and yq leave in ONE sweep
+    // over the accumulator (YQ = 0 stages yq in the y box after its store has been read: a second sweep).  The two boxes cost an
+    // operand stage, which only the epilogue-bound short-K shape can spare.
+    static constexpr int YQ_BYTES = YQ ? 2 * kLnBoxBytes : 0;
     static constexpr int PART_BYTES = 4 * GEMM_BLOCK_M * 8;      // (mean, M2) of the 4 column groups
     static constexpr int COMB_BYTES = GEMM_BLOCK_M * 8;          // this CTA's combined (mean, M2) per row
     static constexpr int RCV_BYTES = 2 * NPAIRS * GEMM_BLOCK_M * 8;  // [tile parity][sender pair][row]
     static constexpr int BAR_BYTES = 512;
-    static constexpr int FIXED_BYTES = 1024 + BAR_BYTES + OUT_BYTES + PART_BYTES + COMB_BYTES + RCV_BYTES;
+    static constexpr int FIXED_BYTES = 1024 + BAR_BYTES + OUT_BYTES + YQ_BYTES + PART_BYTES + COMB_BYTES + RCV_BYTES;
     static constexpr int STAGES_FIT = (kLnSmemLimit - FIXED_BYTES) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES;
     static_assert(STAGES >= 3, "operand ring too shallow");
-    static_assert((2 * STAGES + 4 + 4 * NRING + 2) * 8 + 8 <= BAR_BYTES, "barrier area");
+    static_assert((2 * STAGES + 4 + 4 * NRING + 2 + 4) * 8 + 8 <= BAR_BYTES, "barrier area");
     static_assert(B_BYTES % 1024 == 0, "W tile ends on a swizzle atom");
 };
 
@@ -83,12 +87,12 @@ struct GemmLnParams {
     long long *trace;  // tuning aid: clock64 stamps of block 0's first epilogue thread, 8 per tile (null = off)
 };
 
-template <int NPAIRS, int BNL>
+template <int NPAIRS, int BNL, int YQ>
 __global__ void __launch_bounds__(kLnThreads, 1)
 gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmY,
                const __grid_constant__ CUtensorMap tmYQ, const GemmLnParams p) {
-    using Cfg = GemmLnCfg<NPAIRS, BNL>;
+    using Cfg = GemmLnCfg<NPAIRS, BNL, YQ>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int NBOX = Cfg::NBOX;
     constexpr int NRING = Cfg::NRING;
@@ -97,7 +101,8 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t *ring = smem;
     uint8_t *obuf = smem + STAGES * Cfg::STAGE_BYTES;                       // NBOX boxes, 1024-aligned
-    float2 *part = reinterpret_cast<float2 *>(obuf + Cfg::OUT_BYTES);       // [4][128]
+    uint8_t *yqbuf = obuf + Cfg::OUT_BYTES;                                 // YQ: one box per epilogue team
+    float2 *part = reinterpret_cast<float2 *>(yqbuf + Cfg::YQ_BYTES);       // [4][128]
     float2 *comb = part + 4 * GEMM_BLOCK_M;                                 // [128]
     float2 *rcv = comb + GEMM_BLOCK_M;                                      // [2][NPAIRS][128]
     uint64_t *full_bar = reinterpret_cast<uint64_t *>(rcv + 2 * NPAIRS * GEMM_BLOCK_M);
@@ -109,7 +114,9 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t *ofull_bar = rfree_bar + NRING;     // [NRING] output staged in the box by the 8 warps of its team
     uint64_t *oread_bar = ofull_bar + NRING;     // [NRING] the y store has read the box: the team may stage yq (Q4 models)
     uint64_t *stat_bar = oread_bar + NRING;      // [2] (by tile parity) row statistics of all pairs present
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(stat_bar + 2);
+    uint64_t *yqfull_bar = stat_bar + 2;         // [2] (YQ) yq staged in the team's box by its 8 warps
+    uint64_t *yqread_bar = yqfull_bar + 2;       // [2] (YQ) the yq store has read the team's box
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(yqread_bar + 2);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -131,6 +138,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < STAGES; i++) { mbar_init(&full_bar[i], 2); mbar_init(&empty_bar[i], 1); }
         for (int i = 0; i < 2; i++) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 2 * 16); mbar_init(&stat_bar[i], GEMM_BLOCK_M); }
         for (int i = 0; i < NRING; i++) { mbar_init(&rfull_bar[i], 1); mbar_init(&rfree_bar[i], 1); mbar_init(&ofull_bar[i], 8); mbar_init(&oread_bar[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&yqfull_bar[i], 8); mbar_init(&yqread_bar[i], 1); }
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc<512, 2>(tmem_slot);
@@ -195,10 +203,32 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // ================================================================= TMA-store issuer
         // a warp of its own, so that waiting for a store to finish reading its box (which releases the box to the
         // residual loader, or to the team for the yq copy) never stalls an epilogue warp
-        const uint32_t n_pass = p.qmode ? 2 : 1;
+        const uint32_t n_pass = (p.qmode && !YQ) ? 2 : 1;
         uint32_t iter = 0;
         for (int t = cluster_id; t < m_tiles; t += n_clusters, iter++) {
             const int m0 = t * 2 * GEMM_BLOCK_M + rank * GEMM_BLOCK_M;
+            if (YQ) {  // y from its (in-place) box and yq from the team's box, per column block
+                for (int b = 0; b < NBOX; b++) {
+                    const uint32_t u = iter * NBOX + b, pb = u % NRING, k = u / NRING;
+                    const uint32_t team = (uint32_t)b & 1u;
+                    const uint32_t uq = iter * (uint32_t)((NBOX + 1 - (int)team) / 2) + ((uint32_t)b >> 1);  // uses of the team's box so far
+                    ln_wait(&ofull_bar[pb], k & 1, 10);
+                    if (lane == 0) {
+                        tma_store_2d(&tmY, obuf + pb * kLnBoxBytes, ncol0 + b * GEMM_OUT_BOX_N, m0);
+                        bulk_commit_group();
+                    }
+                    ln_wait(&yqfull_bar[team], uq & 1, 11);
+                    if (lane == 0) {
+                        tma_store_2d(&tmYQ, yqbuf + team * kLnBoxBytes, ncol0 + b * GEMM_OUT_BOX_N, m0);
+                        bulk_commit_group();
+                        bulk_wait_group_read<0>();
+                        mbar_arrive(&rfree_bar[pb]);
+                        mbar_arrive(&yqread_bar[team]);
+                    }
+                    __syncwarp();
+                }
+                continue;
+            }
             for (uint32_t pass = 0; pass < n_pass; pass++)
                 for (int b = 0; b < NBOX; b++) {
                     const uint32_t u = iter * NBOX + b, pb = u % NRING, k = u / NRING;
@@ -326,7 +356,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // Q4 models: sweep 0 stages y for every box of the team, sweep 1 re-reads x from TMEM, normalises again and
             // stages the Q8-rounded copy in the same boxes -- by then the y store of the box has normally been read, so
             // the team does not stall on it (keeping y in registers across the boxes would not fit in 96 registers)
-            const int n_sweep = p.qmode ? 2 : 1;
+            const int n_sweep = (p.qmode && !YQ) ? 2 : 1;
 #pragma unroll 1
             for (int sweep = 0; sweep < n_sweep; sweep++) {
 #pragma unroll 1
@@ -380,6 +410,30 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     fence_proxy_async_smem();  // my generic-proxy writes -> visible to the TMA store
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&ofull_bar[pb]);
+                    if (YQ) {
+                        // the Q8-rounded copy from the same registers (acc still holds the fp32 LayerNorm output) into the team's box
+                        float amax = 0.f;  // as quantize_row_q8_0/1 see it (ggml.c:9493-9509)
+#pragma unroll
+                        for (int j = 0; j < 16; j++) amax = fmaxf(amax, fmaxf(fabsf(__uint_as_float(acc[2 * j])), fabsf(__uint_as_float(acc[2 * j + 1]))));
+                        float id, dq;
+                        q8_scales(amax, p.qmode, id, dq);
+                        const uint32_t uq = iter * (uint32_t)((NBOX + 1 - team) / 2) + ((uint32_t)b >> 1);  // uses of the team's box so far
+                        if (uq >= 1) ln_wait(&yqread_bar[team], (uq - 1) & 1, 12);  // the previous yq store has read it
+                        uint8_t *qbox = yqbuf + team * kLnBoxBytes;
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const float2 v0 = q8_round2(make_float2(__uint_as_float(acc[8 * j + 0]), __uint_as_float(acc[8 * j + 1])), id, dq);
+                            const float2 v1 = q8_round2(make_float2(__uint_as_float(acc[8 * j + 2]), __uint_as_float(acc[8 * j + 3])), id, dq);
+                            const float2 v2 = q8_round2(make_float2(__uint_as_float(acc[8 * j + 4]), __uint_as_float(acc[8 * j + 5])), id, dq);
+                            const float2 v3 = q8_round2(make_float2(__uint_as_float(acc[8 * j + 6]), __uint_as_float(acc[8 * j + 7])), id, dq);
+                            uint4 u4;
+                            u4.x = pack_h2(v0.x, v0.y); u4.y = pack_h2(v1.x, v1.y); u4.z = pack_h2(v2.x, v2.y); u4.w = pack_h2(v3.x, v3.y);
+                            *reinterpret_cast<uint4 *>(qbox + row_off + ((((uint32_t)(half * 4 + j)) ^ sw) << 4)) = u4;
+                        }
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&yqfull_bar[team]);
+                    }
                 }
             }
             if (tracer) { p.trace[iter * 8 + 4] = clock64(); p.trace[iter * 8 + 5] = p.trace[iter * 8 + 4]; }
@@ -398,10 +452,10 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // ------------------------------------------------------------------------------ host side
 bool gemm_ln_supported(int N, int K) { return (N == 384 || N == 768 || N == 1024) && K % 8 == 0 && K >= GEMM_BLOCK_K; }
 
-template <int NPAIRS, int BNL>
+template <int NPAIRS, int BNL, int YQ>
 static cudaError_t launch_ln_cfg(const CUtensorMap &tmA, const CUtensorMap &tmB, const CUtensorMap &tmRes, const CUtensorMap &tmY,
                                  const CUtensorMap &tmYQ, const GemmLnParams &p, int num_sms, cudaStream_t st, int *clusters_out) {
-    using Cfg = GemmLnCfg<NPAIRS, BNL>;
+    using Cfg = GemmLnCfg<NPAIRS, BNL, YQ>;
     constexpr int CSIZE = 2 * NPAIRS;
     static int max_clusters[64] = {0};  // per device: co-resident clusters (GPC boundaries can leave SMs unused)
     int dev = 0;
@@ -417,23 +471,23 @@ static cudaError_t launch_ln_cfg(const CUtensorMap &tmA, const CUtensorMap &tmB,
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     if (!max_clusters[dev]) {
-        cudaError_t err = cudaFuncSetAttribute(gemm_ln_kernel<NPAIRS, BNL>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        cudaError_t err = cudaFuncSetAttribute(gemm_ln_kernel<NPAIRS, BNL, YQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         if (err != cudaSuccess) return err;
         cfg.gridDim = dim3((unsigned)(num_sms / CSIZE * CSIZE));
         int n = 0;
-        err = cudaOccupancyMaxActiveClusters(&n, gemm_ln_kernel<NPAIRS, BNL>, &cfg);
+        err = cudaOccupancyMaxActiveClusters(&n, gemm_ln_kernel<NPAIRS, BNL, YQ>, &cfg);
         if (err != cudaSuccess) return err;
         if (n < 1) return cudaErrorLaunchOutOfResources;
         if (n > num_sms / CSIZE) n = num_sms / CSIZE;
         max_clusters[dev] = n;
-        if (getenv("BERT_B200_DEBUG")) fprintf(stderr, "gemm_ln<%d,%d>: %d co-resident clusters of %d CTAs, %d stages, %d B smem\n", NPAIRS, BNL, n, CSIZE, Cfg::STAGES, Cfg::SMEM_BYTES);
+        if (getenv("BERT_B200_DEBUG")) fprintf(stderr, "gemm_ln<%d,%d,%d>: %d co-resident clusters of %d CTAs, %d stages, %d B smem\n", NPAIRS, BNL, YQ, n, CSIZE, Cfg::STAGES, Cfg::SMEM_BYTES);
     }
     if (clusters_out) *clusters_out = max_clusters[dev];
     const int m_tiles = (p.M + 2 * GEMM_BLOCK_M - 1) / (2 * GEMM_BLOCK_M);
     if (m_tiles < 1) return cudaSuccess;
     const int clusters = m_tiles < max_clusters[dev] ? m_tiles : max_clusters[dev];
     cfg.gridDim = dim3((unsigned)(clusters * CSIZE));
-    return cudaLaunchKernelEx(&cfg, gemm_ln_kernel<NPAIRS, BNL>, tmA, tmB, tmRes, tmY, tmYQ, p);
+    return cudaLaunchKernelEx(&cfg, gemm_ln_kernel<NPAIRS, BNL, YQ>, tmA, tmB, tmRes, tmY, tmYQ, p);
 }
 
 static long long *g_ln_trace = nullptr;
@@ -447,9 +501,16 @@ cudaError_t launch_gemm_ln(const CUtensorMap &tmA, const WeightMaps &W, const CU
     p.M = M; p.N = N; p.K = K; p.bias = bias; p.gamma = gamma; p.beta = beta; p.eps = eps; p.qmode = qmode; p.trace = g_ln_trace;
     const CUtensorMap &tq = tmYQ ? *tmYQ : tmY;
     // WeightMaps::tm index: box heights 32/64/96/128/192/256 rows; a CTA loads BNL/2 rows of W per K block
-    if (N == 384) return launch_ln_cfg<2, 192>(tmA, W.tm[2], tmRes, tmY, tq, p, num_sms, st, nullptr);
-    if (N == 768) return launch_ln_cfg<3, 256>(tmA, W.tm[3], tmRes, tmY, tq, p, num_sms, st, nullptr);
-    return launch_ln_cfg<4, 256>(tmA, W.tm[3], tmRes, tmY, tq, p, num_sms, st, nullptr);
+    // Q4 models, short K (the attention-output projection): the epilogue is the bottleneck -> single-sweep variant
+    static const int yq_max_k = [] { const char *v = getenv("BERT_B200_LN_YQ_K"); return v ? atoi(v) : 1024; }();
+    if (qmode && K <= yq_max_k) {
+        if (N == 384) return launch_ln_cfg<2, 192, 1>(tmA, W.tm[2], tmRes, tmY, tq, p, num_sms, st, nullptr);
+        if (N == 768) return launch_ln_cfg<3, 256, 1>(tmA, W.tm[3], tmRes, tmY, tq, p, num_sms, st, nullptr);
+        return launch_ln_cfg<4, 256, 1>(tmA, W.tm[3], tmRes, tmY, tq, p, num_sms, st, nullptr);
+    }
+    if (N == 384) return launch_ln_cfg<2, 192, 0>(tmA, W.tm[2], tmRes, tmY, tq, p, num_sms, st, nullptr);
+    if (N == 768) return launch_ln_cfg<3, 256, 0>(tmA, W.tm[3], tmRes, tmY, tq, p, num_sms, st, nullptr);
+    return launch_ln_cfg<4, 256, 0>(tmA, W.tm[3], tmRes, tmY, tq, p, num_sms, st, nullptr);
 }
 
 }  // namespace bk
