@@ -276,6 +276,7 @@ __global__ void __launch_bounds__(256) pool_norm_kernel(const __half *__restrict
     for (int c = c0; c < nch; c += cpr) {
         float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (g < groups) {
+#pragma unroll 8  // the loads of 8 tokens in flight together (same summation order): a one-sentence launch is latency bound
             for (int t = t0 + g; t < t1; t += groups) {
                 const uint4 u = __ldg(reinterpret_cast<const uint4 *>(x + (size_t)t * d) + c);
                 float2 f;
