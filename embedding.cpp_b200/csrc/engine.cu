@@ -104,7 +104,10 @@ struct bk_engine {
     // staged batch
     int st_T = 0, st_nseq = 0, st_maxlen = 0;  // last forward (hidden-state readback)
     // staged set (bench `value` leg): a whole job resident in HBM, cut into micro-batches of <= cap_tokens
-    struct Slice { int tok_off, seq_off, T, n_seq, max_len; };
+    // n_long / max_short: the sentences of more than 128 tokens form the first n_long of the slice (length-sorted input) and the
+    // longest of the others has max_short tokens -> attention runs as two launches, each with the kernel made for its lengths;
+    // n_long = 0: one launch for all
+    struct Slice { int tok_off, seq_off, T, n_seq, max_len, n_long, max_short; };
     std::vector<Slice> slices;
     int32_t *sg_tokens = nullptr, *sg_lens = nullptr;
     float *sg_out = nullptr;
@@ -114,7 +117,7 @@ struct bk_engine {
     bool keep_hidden = false;
     __half *hidden = nullptr;  // [n_layer+1][cap_tokens][d]
     // CUDA graphs of the launch plan for small batches (latency path): key = (T, n_seq, max_len)
-    struct GraphEntry { int T, n_seq, max_len, slot; cudaGraphExec_t exec; uint64_t last_use; };
+    struct GraphEntry { int T, n_seq, max_len, n_long, max_short, slot; cudaGraphExec_t exec; uint64_t last_use; };
     std::vector<GraphEntry> graphs;
     uint64_t graph_clock = 0;
     int graph_max_tokens = 4096;  // BERT_B200_GRAPH_TOKENS; 0 disables
@@ -393,7 +396,8 @@ int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const WeightMaps &W
 }
 
 // all kernels of one batch already resident on the device (tokens, lens in d_tokens/d_lens)
-int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens, int T, int n_seq, int max_len, float *d_out) {
+int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens, int T, int n_seq, int max_len, int n_long, int max_short,
+                   float *d_out) {
     const bk_hparams &hp = e->hp;
     const int d = hp.n_embd, f = hp.n_intermediate;
     const int q = e->qmode;
@@ -418,8 +422,14 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
         if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, L.pqkv, T, 3 * d, d, L.bqkv, nullptr, e->to_qkv, BK_EPI_BIAS)) return -1;
         {
             KTimer t(e, BK_K_ATTN);
-            CK(launch_attention(e->ta_qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
-            e->launch_count++;
+            if (n_long > 0 && n_long < n_seq) {  // long sentences: streaming kernel; the rest: one CTA per (sentence, head)
+                CK(launch_attention(e->ta_qkv, e->d_cu, n_long, max_len, d, hp.n_head, e->att, q, e->st));
+                CK(launch_attention(e->ta_qkv, e->d_cu + n_long, n_seq - n_long, max_short, d, hp.n_head, e->att, q, e->st));
+                e->launch_count += 2;
+            } else {
+                CK(launch_attention(e->ta_qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
+                e->launch_count++;
+            }
         }
         const bool fused_ln = e->fused_ln_tokens >= 0 && T > e->fused_ln_tokens && gemm_ln_supported(d, d) && gemm_ln_supported(d, f);
         if (fused_ln) {  // y = LN(att.Wo^T + bo + x) in one kernel (tr_y doubles as the output map of y: same box geometry)
@@ -457,10 +467,10 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
 
 // the same launch sequence captured once per (T, n_seq, max_len) and replayed (kernel arguments -- sizes, tensor
 // maps, engine-owned device pointers -- are identical for equal keys); least-recently-used of 32 shapes is evicted
-int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len) {
+int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, int n_long, int max_short) {
     e->graph_clock++;
     for (auto &g : e->graphs)
-        if (g.T == T && g.n_seq == n_seq && g.max_len == max_len && g.slot == slot) {
+        if (g.T == T && g.n_seq == n_seq && g.max_len == max_len && g.n_long == n_long && g.max_short == max_short && g.slot == slot) {
             g.last_use = e->graph_clock;
             CK(cudaGraphLaunch(g.exec, e->st));
             e->launch_count += 4 + 7 * e->hp.n_layer;
@@ -468,7 +478,7 @@ int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len) {
         }
     cudaGraph_t graph = nullptr;
     CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
-    const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, max_len, e->d_out2[slot]);
+    const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, max_len, n_long, max_short, e->d_out2[slot]);
     const cudaError_t ce = cudaStreamEndCapture(e->st, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (ce != cudaSuccess) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(ce));
@@ -482,9 +492,23 @@ int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len) {
         cudaGraphExecDestroy(e->graphs[lru].exec);
         e->graphs.erase(e->graphs.begin() + (long)lru);
     }
-    e->graphs.push_back({T, n_seq, max_len, slot, exec, e->graph_clock});
+    e->graphs.push_back({T, n_seq, max_len, n_long, max_short, slot, exec, e->graph_clock});
     CK(cudaGraphLaunch(exec, e->st));
     return 0;
+}
+
+// sentences of more than 128 tokens first?  -> their count and the longest of the rest; otherwise (or when there are none, or
+// nothing else) n_long = 0
+void split_by_length(const int32_t *lens, int n_seq, int *n_long, int *max_short) {
+    int nl = 0, ms = 0;
+    while (nl < n_seq && lens[nl] > 128) nl++;
+    for (int i = nl; i < n_seq; i++) {
+        if (lens[i] > 128) { *n_long = 0; *max_short = 0; return; }  // not sorted: one launch
+        if (lens[i] > ms) ms = lens[i];
+    }
+    if (nl == n_seq) nl = 0;
+    *n_long = nl;
+    *max_short = nl ? ms : 0;
 }
 
 int check_batch(bk_engine *e, const int32_t *lens, int n_seq, int *T_out, int *maxlen_out) {
@@ -515,7 +539,7 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
     e->slices.clear();
     long long total = 0;
     for (int i = 0; i < n_seq;) {
-        bk_engine::Slice sl{(int)total, i, 0, 0, 0};
+        bk_engine::Slice sl{(int)total, i, 0, 0, 0, 0, 0};
         while (i < n_seq && sl.n_seq < e->cap_seqs) {
             if (lens[i] < 1 || lens[i] > e->hp.n_max_tokens) return fail("sentence %d has %d tokens (allowed 1..%d)", i, lens[i], e->hp.n_max_tokens);
             if (sl.T + lens[i] > e->cap_tokens) break;
@@ -524,6 +548,7 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
             i++;
         }
         total += sl.T;
+        split_by_length(lens + sl.seq_off, sl.n_seq, &sl.n_long, &sl.max_short);
         e->slices.push_back(sl);
     }
     if ((size_t)total > e->sg_cap_tokens || (size_t)n_seq > e->sg_cap_seqs) {
@@ -551,10 +576,12 @@ BK_API int bk_engine_submit(bk_engine *e, int32_t slot, const int32_t *tokens, c
     CK(cudaMemcpyAsync(e->d_tokens2[slot], e->h_tokens2[slot], (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
     CK(cudaMemcpyAsync(e->d_lens2[slot], e->h_lens2[slot], (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
     e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
+    int n_long = 0, max_short = 0;
+    split_by_length(lens, n_seq, &n_long, &max_short);
     if (T <= e->graph_max_tokens && !e->keep_hidden && !e->timing) {
         // small batch: the 3 + 7*n_layer + 1 launches cost more host time than GPU time -> replay a captured graph
-        if (forward_graph(e, slot, T, n_seq, mx)) return -1;
-    } else if (forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, e->d_out2[slot])) return -1;
+        if (forward_graph(e, slot, T, n_seq, mx, n_long, max_short)) return -1;
+    } else if (forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot])) return -1;
     CK(cudaMemcpyAsync(e->h_out2[slot], e->d_out2[slot], (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
     CK(cudaEventRecord(e->slot_done[slot], e->st));
     e->slot_nseq[slot] = n_seq;
@@ -590,7 +617,7 @@ BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernel
     for (int i = 0; i < iters && rc == 0; i++)
         for (const auto &sl : e->slices) {
             e->st_T = sl.T; e->st_nseq = sl.n_seq; e->st_maxlen = sl.max_len;
-            rc = forward_device(e, e->sg_tokens + sl.tok_off, e->sg_lens + sl.seq_off, sl.T, sl.n_seq, sl.max_len,
+            rc = forward_device(e, e->sg_tokens + sl.tok_off, e->sg_lens + sl.seq_off, sl.T, sl.n_seq, sl.max_len, sl.n_long, sl.max_short,
                                 e->sg_out + (size_t)sl.seq_off * e->hp.n_embd);
             if (rc) break;
         }
