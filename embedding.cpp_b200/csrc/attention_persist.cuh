@@ -55,6 +55,7 @@ attention_persist_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_local = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // grid <= n_items
     constexpr int CW = 4;
+    pdl_launch_dependents();
     if (warp == CW) {
         if (lane == 0) {
             tma_prefetch_desc(&tmQKV);
@@ -73,6 +74,7 @@ attention_persist_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // set-up done under the previous kernel's tail; global memory (sequence bounds, qkv, out) from here on
 
     if (warp == CW) {
         // ================================================================ control warp (uniform, elected issue)
@@ -318,7 +320,7 @@ static cudaError_t launch_att_persist(const CUtensorMap &tm, const int32_t *cu, 
     const int n_items = n_seq * n_head;
     const int grid = n_items < 2 * sms[dev] ? n_items : 2 * sms[dev];
     const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934
-    attention_persist_kernel<DH><<<grid, kPersistThreads, Cfg::SMEM, st>>>(tm, cu, d, n_head, n_items, out, qmode, scale);
-    return cudaGetLastError();
+    LaunchConfig lc(dim3((unsigned)grid), dim3(kPersistThreads), Cfg::SMEM, st);
+    return cudaLaunchKernelEx(&lc.cfg, attention_persist_kernel<DH>, tm, cu, d, n_head, n_items, out, qmode, scale);
 }
 

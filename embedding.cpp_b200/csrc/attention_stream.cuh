@@ -46,6 +46,8 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
     extern __shared__ __align__(1024) uint8_t att_raw[];
     uint8_t *smem = att_raw;
 
+    pdl_launch_dependents();
+    pdl_wait();  // the sequence bounds are read first thing
     const int seq = blockIdx.z, head = blockIdx.y;
     const int t0 = __ldg(cu + seq);
     const int L = __ldg(cu + seq + 1) - t0;
@@ -354,6 +356,6 @@ static cudaError_t launch_att_stream(const CUtensorMap &tm, const int32_t *cu, i
     }
     dim3 grid(1, n_head, n_seq);
     const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934
-    attention_stream_kernel<DH><<<grid, kStreamThreads, smem, st>>>(tm, cu, d, out, qmode, scale);
-    return cudaGetLastError();
+    LaunchConfig lc(grid, dim3(kStreamThreads), smem, st);
+    return cudaLaunchKernelEx(&lc.cfg, attention_stream_kernel<DH>, tm, cu, d, out, qmode, scale);
 }

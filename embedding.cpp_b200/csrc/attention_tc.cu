@@ -87,6 +87,8 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
     constexpr int PBUF = kAttQ * 128;      // one P chunk: 128 rows x 64 keys f16
     extern __shared__ __align__(1024) uint8_t att_raw[];  // swizzle atoms need 1024-byte alignment; no static shared memory in this kernel
     uint8_t *smem = att_raw;
+    pdl_launch_dependents();
+    pdl_wait();  // the sequence bounds are read first thing
 
     const int seq = blockIdx.z, head = blockIdx.y;
     const int t0 = __ldg(cu + seq);
@@ -403,8 +405,8 @@ static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_se
     }
     dim3 grid(1, n_head, n_seq);
     const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934: 1.0f/sqrt((float)dh) evaluated in double
-    attention_tc_kernel<DH, G><<<grid, 32 + 128 * G, smem, st>>>(tm, cu, d, out, qmode, scale, multi);
-    return cudaGetLastError();
+    LaunchConfig lc(grid, dim3(32 + 128 * G), smem, st);
+    return cudaLaunchKernelEx(&lc.cfg, attention_tc_kernel<DH, G>, tm, cu, d, out, qmode, scale, multi);
 }
 
 cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens, int n_seq, int max_len, int d, int n_head,

@@ -30,6 +30,17 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// With cudaLaunchAttributeProgrammaticStreamSerialization (the engine sets it for the small-batch launch plan, see
+// kernels.h) the next kernel of the stream may become resident once every CTA of this one has executed
+// launch_dependents, and runs its prologue (barrier init, TMEM allocation, descriptor prefetch) under this kernel's
+// tail; griddepcontrol.wait then blocks until this grid has completed and its memory is visible.  Rule in this code
+// base: launch_dependents first thing, wait before the first access to global memory other than kernel parameters --
+// reads (a chain of prologues can be in flight: data of ANY earlier kernel may still be on its way) and writes (an earlier
+// kernel may still be reading the buffer).  Both are no-ops in a launch without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ------------------------------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

@@ -478,7 +478,12 @@ int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, int n_l
         }
     cudaGraph_t graph = nullptr;
     CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
+    // the latency path: kernel boundaries become programmatic dependencies, so every kernel's set-up (and its launch) runs
+    // under the tail of the one before it (common.cuh: pdl_wait).  BERT_B200_PDL=0 captures plain edges.
+    static const bool use_pdl = [] { const char *v = getenv("BERT_B200_PDL"); return !v || atoi(v) != 0; }();
+    pdl_flag() = use_pdl;
     const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, max_len, n_long, max_short, e->d_out2[slot]);
+    pdl_flag() = false;
     const cudaError_t ce = cudaStreamEndCapture(e->st, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (ce != cudaSuccess) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(ce));

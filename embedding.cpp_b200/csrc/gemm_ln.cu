@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(kLnThreads, 1)
 gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmY,
                const __grid_constant__ CUtensorMap tmYQ, const GemmLnParams p) {
+    pdl_launch_dependents();
     using Cfg = GemmLnCfg<NPAIRS, BNL, YQ>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int NBOX = Cfg::NBOX;
@@ -146,6 +147,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // prologue done under the previous kernel's tail; global memory from here on
 
     if (warp == 0) {
         // ===================================================================== TMA producer (A, W)
@@ -461,15 +463,8 @@ static cudaError_t launch_ln_cfg(const CUtensorMap &tmA, const CUtensorMap &tmB,
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    cudaLaunchConfig_t cfg = {};
-    cfg.blockDim = dim3(kLnThreads);
-    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CSIZE; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    LaunchConfig lc(dim3(1), dim3(kLnThreads), Cfg::SMEM_BYTES, st, CSIZE);
+    cudaLaunchConfig_t &cfg = lc.cfg;
     if (!max_clusters[dev]) {
         cudaError_t err = cudaFuncSetAttribute(gemm_ln_kernel<NPAIRS, BNL, YQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         if (err != cudaSuccess) return err;

@@ -132,6 +132,7 @@ template <int BN, int CG, int WQ>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes, const GemmParams p) {
+    pdl_launch_dependents();
     using Cfg = GemmCfg<BN, CG, WQ>;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int NBOX = Cfg::NBOX;
@@ -180,34 +181,62 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (warp != 0) pdl_wait();  // everything above ran under the previous kernel's tail; from here on global memory is touched
 
     // Warps 0-2 run their loops with all 32 lanes in uniform control flow and issue through the *_e
     // ("elected lane") wrappers -- see common.cuh for why.
     if (warp == 0) {
         // ===================================================================== TMA producer (A, W)
+        // The weights do not depend on the previous kernel: the W tiles of the first K blocks of this CTA's first tile
+        // are requested BEFORE the grid dependency resolves (programmatic dependent launch, common.cuh), the activations
+        // after it.  In the one-sentence regime a projection is mostly the time to stream its weights.
+        const int n_pre = num_kb < STAGES ? num_kb : STAGES;  // stages filled ahead (the ring is empty: no wait)
+        {
+            const int n0 = (unit % n_tiles) * BN + rank * Cfg::B_ROWS;
+            for (int kb = 0; kb < n_pre; kb++) {
+                uint8_t *sb = ring + kb * Cfg::STAGE_BYTES + Cfg::A_BYTES;
+                if (WQ) {
+                    const int rows = p.N - n0 < BN ? p.N - n0 : BN;  // multiple of 32 -> bytes multiple of 16
+                    const uint32_t bytes = (uint32_t)(rows * Cfg::PK_ROWB);
+                    mbar_expect_tx_e(&pkfull_bar[kb], bytes);
+                    bulk_load_1d_e(sb + Cfg::B_BYTES, p.wq + ((size_t)kb * p.N + n0) * Cfg::PK_ROWB, bytes, &pkfull_bar[kb]);
+                } else if (CG == 1) {
+                    mbar_expect_tx_e(&full_bar[kb], Cfg::A_BYTES + Cfg::B_BYTES);
+                    tma_load_2d_e(sb, &tmB, &full_bar[kb], kb * GEMM_BLOCK_K, n0);
+                } else {
+                    const uint32_t lead_full = smem_u32(&full_bar[kb]) & kPeerBitMask;
+                    mbar_arrive_expect_tx_cluster_e(lead_full, Cfg::A_BYTES + Cfg::B_BYTES);
+                    tma_load_2d_pair_e(sb, &tmB, lead_full, kb * GEMM_BLOCK_K, n0);
+                }
+            }
+        }
+        pdl_wait();
         int s = 0; uint32_t ph = 0;
         for (int t = unit; t < num_tiles; t += units) {
             const int m0 = (t / n_tiles) * TILE_M + rank * GEMM_BLOCK_M, n0 = (t % n_tiles) * BN + rank * Cfg::B_ROWS;
             for (int kb = 0; kb < num_kb; kb++) {
+                const bool w_ahead = t == unit && kb < n_pre;  // W (and the barrier's byte count) already under way
                 mbar_wait(&empty_bar[s], ph ^ 1);
                 uint8_t *sa = ring + s * Cfg::STAGE_BYTES, *sb = sa + Cfg::A_BYTES;
                 if (WQ) {
                     mbar_expect_tx_e(&full_bar[s], Cfg::A_BYTES);
                     tma_load_2d_e(sa, &tmA, &full_bar[s], kb * GEMM_BLOCK_K, m0);
-                    const int rows = p.N - n0 < BN ? p.N - n0 : BN;  // multiple of 32 -> bytes multiple of 16
-                    const uint32_t bytes = (uint32_t)(rows * Cfg::PK_ROWB);
-                    mbar_expect_tx_e(&pkfull_bar[s], bytes);
-                    bulk_load_1d_e(sb + Cfg::B_BYTES, p.wq + ((size_t)kb * p.N + n0) * Cfg::PK_ROWB, bytes, &pkfull_bar[s]);
+                    if (!w_ahead) {
+                        const int rows = p.N - n0 < BN ? p.N - n0 : BN;  // multiple of 32 -> bytes multiple of 16
+                        const uint32_t bytes = (uint32_t)(rows * Cfg::PK_ROWB);
+                        mbar_expect_tx_e(&pkfull_bar[s], bytes);
+                        bulk_load_1d_e(sb + Cfg::B_BYTES, p.wq + ((size_t)kb * p.N + n0) * Cfg::PK_ROWB, bytes, &pkfull_bar[s]);
+                    }
                 } else if (CG == 1) {
-                    mbar_expect_tx_e(&full_bar[s], Cfg::A_BYTES + Cfg::B_BYTES);
+                    if (!w_ahead) mbar_expect_tx_e(&full_bar[s], Cfg::A_BYTES + Cfg::B_BYTES);
                     tma_load_2d_e(sa, &tmA, &full_bar[s], kb * GEMM_BLOCK_K, m0);
-                    tma_load_2d_e(sb, &tmB, &full_bar[s], kb * GEMM_BLOCK_K, n0);
+                    if (!w_ahead) tma_load_2d_e(sb, &tmB, &full_bar[s], kb * GEMM_BLOCK_K, n0);
                 } else {
                     // both CTAs report to the leader's barrier: one arrival + this CTA's bytes each
                     const uint32_t lead_full = smem_u32(&full_bar[s]) & kPeerBitMask;
-                    mbar_arrive_expect_tx_cluster_e(lead_full, Cfg::A_BYTES + Cfg::B_BYTES);
+                    if (!w_ahead) mbar_arrive_expect_tx_cluster_e(lead_full, Cfg::A_BYTES + Cfg::B_BYTES);
                     tma_load_2d_pair_e(sa, &tmA, lead_full, kb * GEMM_BLOCK_K, m0);
-                    tma_load_2d_pair_e(sb, &tmB, lead_full, kb * GEMM_BLOCK_K, n0);
+                    if (!w_ahead) tma_load_2d_pair_e(sb, &tmB, lead_full, kb * GEMM_BLOCK_K, n0);
                 }
                 if (++s == STAGES) { s = 0; ph ^= 1; }
             }
@@ -454,17 +483,8 @@ static cudaError_t launch_cfg(const CUtensorMap &tmA, const WeightMaps &W, const
     const int max_grid = num_sms / CG * CG;
     if (grid > max_grid) grid = max_grid;
     if (grid < 1) return cudaSuccess;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)grid);
-    cfg.blockDim = dim3(kGemmThreads);
-    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, CG, WQ>, tmA, W.tm[bi], tmOut, tmRes, p);
+    LaunchConfig lc(dim3((unsigned)grid), dim3(kGemmThreads), Cfg::SMEM_BYTES, st, CG);
+    return cudaLaunchKernelEx(&lc.cfg, gemm_tcgen05_kernel<BN, CG, WQ>, tmA, W.tm[bi], tmOut, tmRes, p);
 }
 
 static inline const CUtensorMap &tmR0(const CUtensorMap *tmRes, const CUtensorMap &tmOut) { return tmRes ? *tmRes : tmOut; }

@@ -7,6 +7,30 @@
 
 namespace bk {
 
+// Programmatic dependent launch (common.cuh): on for the launches of the calling thread while the engine captures the
+// small-batch launch plan.  Every kernel of that plan is launched through launch_config(), which adds the attribute.
+inline bool &pdl_flag() { static thread_local bool on = false; return on; }
+struct LaunchConfig {
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[2];
+    LaunchConfig(dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster = 0) : cfg{} {
+        cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        unsigned n = 0;
+        if (cluster > 0) {
+            attr[n].id = cudaLaunchAttributeClusterDimension;
+            attr[n].val.clusterDim.x = (unsigned)cluster; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
+            n++;
+        }
+        if (pdl_flag()) {
+            attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[n].val.programmaticStreamSerializationAllowed = 1;
+            n++;
+        }
+        cfg.attrs = attr;
+        cfg.numAttrs = n;
+    }
+};
+
 // ---- gemm_tcgen05.cu ------------------------------------------------------------------------
 // out[M][N] = epi(A[M][K] . W[N][K]^T + bias (+ resid))   A, W, out, resid: f16, fp32 accumulation in TMEM.
 struct GemmParams {

@@ -21,6 +21,8 @@ constexpr int kMaxChunks = 8;  // 8 halves per chunk, 32 lanes -> d <= 2048
 // lens[n_seq] -> cu[n_seq+1]; pos[t] = t - cu[seq(t)].  Single CTA scan (n_seq is at most a few
 // thousand per launch), then all CTAs fill positions by binary search over cu.
 __global__ void pack_scan_kernel(const int32_t *__restrict__ lens, int n_seq, int32_t *__restrict__ cu) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ int32_t warp_tot[32];
     __shared__ int32_t carry_s;
     if (threadIdx.x == 0) { carry_s = 0; cu[0] = 0; }
@@ -55,6 +57,8 @@ __global__ void pack_scan_kernel(const int32_t *__restrict__ lens, int n_seq, in
     }
 }
 __global__ void pack_pos_kernel(const int32_t *__restrict__ cu, int n_seq, int32_t *__restrict__ pos, int T) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= T) return;
     int lo = 0, hi = n_seq;  // find s with cu[s] <= t < cu[s+1]
@@ -65,8 +69,16 @@ __global__ void pack_pos_kernel(const int32_t *__restrict__ cu, int n_seq, int32
     pos[t] = t - __ldg(cu + lo);
 }
 cudaError_t launch_pack(const int32_t *lens, int n_seq, int32_t *cu_seqlens, int32_t *pos, int T, cudaStream_t st) {
-    pack_scan_kernel<<<1, 1024, 0, st>>>(lens, n_seq, cu_seqlens);
-    pack_pos_kernel<<<(T + 255) / 256, 256, 0, st>>>(cu_seqlens, n_seq, pos, T);
+    {
+        LaunchConfig lc(dim3(1), dim3(1024), 0, st);
+        cudaError_t err = cudaLaunchKernelEx(&lc.cfg, pack_scan_kernel, lens, n_seq, cu_seqlens);
+        if (err != cudaSuccess) return err;
+    }
+    {
+        LaunchConfig lc(dim3((unsigned)((T + 255) / 256)), dim3(256), 0, st);
+        cudaError_t err = cudaLaunchKernelEx(&lc.cfg, pack_pos_kernel, (const int32_t *)cu_seqlens, n_seq, pos, T);
+        if (err != cudaSuccess) return err;
+    }
     return cudaGetLastError();
 }
 
@@ -170,6 +182,8 @@ __device__ __forceinline__ void ln_store(float (&v)[NIT][8], int d, float eps, c
 // ------------------------------------------------------------------------------- embed + LN
 template <bool kWriteQ, int NIT>
 __global__ void __launch_bounds__(256) embed_ln_kernel(const EmbedParams p) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (t >= p.T) return;
     const int lane = lane_id();
@@ -199,8 +213,9 @@ cudaError_t launch_embed_ln(const EmbedParams &p, cudaStream_t st) {
     const int nit = (p.d + 255) / 256;  // 16-byte chunks per lane
 #define BK_EMBED(NIT)                                                        \
     do {                                                                     \
-        if (p.qmode) embed_ln_kernel<true, NIT><<<grid, wpb * 32, 0, st>>>(p); \
-        else embed_ln_kernel<false, NIT><<<grid, wpb * 32, 0, st>>>(p);        \
+        LaunchConfig lc(dim3((unsigned)grid), dim3((unsigned)(wpb * 32)), 0, st);                          \
+        if (p.qmode) cudaLaunchKernelEx(&lc.cfg, embed_ln_kernel<true, NIT>, p);  \
+        else cudaLaunchKernelEx(&lc.cfg, embed_ln_kernel<false, NIT>, p);         \
     } while (0)
     if (nit <= 1) BK_EMBED(1);
     else if (nit == 2) BK_EMBED(2);
@@ -216,6 +231,8 @@ template <bool kWriteQ, int NIT>
 __global__ void __launch_bounds__(256) add_ln_kernel(const __half *__restrict__ pre, const float *__restrict__ gamma,
                                                      const float *__restrict__ beta, int T, int d, float eps,
                                                      __half *__restrict__ y, __half *__restrict__ yq, int qmode) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (t >= T) return;
     const int lane = lane_id();
@@ -245,8 +262,9 @@ cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *be
     const int nit = (d + 255) / 256;  // 16-byte chunks per lane
 #define BK_ADDLN(NIT)                                                                                          \
     do {                                                                                                       \
-        if (qmode) add_ln_kernel<true, NIT><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, qmode); \
-        else add_ln_kernel<false, NIT><<<grid, wpb * 32, 0, st>>>(pre, gamma, beta, T, d, eps, y, yq, 0);          \
+        LaunchConfig lc(dim3((unsigned)grid), dim3((unsigned)(wpb * 32)), 0, st);                                     \
+        if (qmode) cudaLaunchKernelEx(&lc.cfg, add_ln_kernel<true, NIT>, pre, gamma, beta, T, d, eps, y, yq, qmode); \
+        else cudaLaunchKernelEx(&lc.cfg, add_ln_kernel<false, NIT>, pre, gamma, beta, T, d, eps, y, yq, 0);         \
     } while (0)
     if (nit <= 1) BK_ADDLN(1);
     else if (nit == 2) BK_ADDLN(2);
@@ -262,6 +280,8 @@ cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *be
 // bert.cpp:999-1001), out = e * (1/sqrt(sum e^2)) (bert.cpp:1004-1006).
 __global__ void __launch_bounds__(256) pool_norm_kernel(const __half *__restrict__ x, const int32_t *__restrict__ cu,
                                                         int d, float *__restrict__ out) {
+    pdl_launch_dependents();
+    pdl_wait();
     extern __shared__ float sacc[];  // [ngroups][d]
     __shared__ float red[8];
     const int s = blockIdx.x;
@@ -312,7 +332,8 @@ cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, int n_s
     const int cpr = nch < 256 ? nch : 256;
     const int groups = 256 / cpr > 0 ? 256 / cpr : 1;
     const size_t smem = (size_t)groups * d * sizeof(float);
-    pool_norm_kernel<<<n_seq, 256, smem, st>>>(x, cu_seqlens, d, out);
+    LaunchConfig lc(dim3((unsigned)n_seq), dim3(256), smem, st);
+    cudaLaunchKernelEx(&lc.cfg, pool_norm_kernel, x, cu_seqlens, d, out);
     return cudaGetLastError();
 }
 
