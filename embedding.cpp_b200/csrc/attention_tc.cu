@@ -128,6 +128,19 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
             for (int i = 0; i < 4; i++) { mbar_init(&pfull[i], 4 * (G >= 2 ? 2 : 1)); mbar_init(&pfree[i], 1); }
             mbar_fence_init();
         }
+        __syncwarp();
+        {
+            // the loads first: they need the barriers only, and their latency then runs under the TMEM allocation and the CTA-wide
+            // synchronisation below
+            const int cq = head * DH, ck = d + head * DH, cv = 2 * d + head * DH;
+            mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
+            tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, t0);
+            tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, t0 + 64);
+            mbar_expect_tx_e(bar_k, (uint32_t)(Lk64 * ROWB));
+            for (int c = 0; c < n_chunks; c++) tma_load_2d_e(sK + c * 64 * ROWB, &tmQKV, bar_k, ck, t0 + c * 64);
+            mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
+            for (int c = 0; c < n_chunks; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
+        }
         for (int i = lane; i < 128; i += 32) ones[i] = 0x3C003C00u;
         fence_proxy_async_smem();
         __syncwarp();
@@ -146,14 +159,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
 
     if (warp == CW) {
         // ================================================================ control warp (uniform, elected issue)
-        const int cq = head * DH, ck = d + head * DH, cv = 2 * d + head * DH;
-        mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
-        tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, t0);
-        tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, t0 + 64);
-        mbar_expect_tx_e(bar_k, (uint32_t)(Lk64 * ROWB));
-        for (int c = 0; c < n_chunks; c++) tma_load_2d_e(sK + c * 64 * ROWB, &tmQKV, bar_k, ck, t0 + c * 64);
-        mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
-        for (int c = 0; c < n_chunks; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
+        const int cq = head * DH;  // (Q, K, V of the first block were requested in the prologue)
 
         const uint32_t idesc_pv = att_idesc(DH, 1);
         // S = Q . K^T for key columns [n_lo, n_hi): instructions of <= 256 columns
