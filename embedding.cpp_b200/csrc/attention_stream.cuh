@@ -90,6 +90,28 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
             for (int i = 0; i < 4; i++) { mbar_init(&pfull[i], 8); mbar_init(&pfree[i], 1); }
             mbar_fence_init();
         }
+        __syncwarp();
+        {
+            // the loads first (they need the barriers only): their latency runs under the TMEM allocation and the CTA-wide sync
+            const int cq = head * DH, ck = d + head * DH, cv = 2 * d + head * DH;
+            const int n_box = Lk64 >> 6;
+            mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
+            tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, t0);
+            tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, t0 + 64);
+            for (int c = 0; c < nc; c++) {  // K in chunks of 128 keys (two 64-row boxes, the last chunk possibly one)
+                const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
+                mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
+                for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, t0 + (2 * c + b) * 64);
+            }
+            if (nqb > 1) {
+                uint8_t *q1 = sQ + kAttQ * ROWB;
+                mbar_expect_tx_e(&bar_q[1], (uint32_t)(kAttQ * ROWB));
+                tma_load_2d_e(q1, &tmQKV, &bar_q[1], cq, t0 + kAttQ);
+                tma_load_2d_e(q1 + 64 * ROWB, &tmQKV, &bar_q[1], cq, t0 + kAttQ + 64);
+            }
+            mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
+            for (int c = 0; c < n_box; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
+        }
         for (int i = lane; i < 128; i += 32) ones[i] = 0x3C003C00u;
         fence_proxy_async_smem();
         __syncwarp();
@@ -102,8 +124,7 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
 
     if (warp == CW) {
         // ================================================================ score warp: TMA loads, S = Q . K^T jobs
-        const int cq = head * DH, ck = d + head * DH, cv = 2 * d + head * DH;
-        const int n_box = Lk64 >> 6;
+        const int cq = head * DH;  // (Q(0), Q(1), K and V were requested in the prologue)
         auto load_q = [&](int qb) {  // query block qb -> Q buffer qb % 2
             uint8_t *q = sQ + (qb % kStreamQ) * kAttQ * ROWB;
             uint64_t *bar = &bar_q[qb % kStreamQ];
@@ -111,15 +132,6 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t
             tma_load_2d_e(q, &tmQKV, bar, cq, t0 + qb * kAttQ);
             tma_load_2d_e(q + 64 * ROWB, &tmQKV, bar, cq, t0 + qb * kAttQ + 64);
         };
-        load_q(0);
-        for (int c = 0; c < nc; c++) {  // K in chunks of 128 keys (two 64-row boxes, the last chunk possibly one)
-            const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
-            mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
-            for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, t0 + (2 * c + b) * 64);
-        }
-        if (nqb > 1) load_q(1);
-        mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
-        for (int c = 0; c < n_box; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
 
         // score jobs in the order the softmax warps consume them: A(0,0..nc-1), then B(q,c) A(q+1,c) for c = 0..nc-1, q = 0..
         const int n_jobs = 2 * nqb * nc;
