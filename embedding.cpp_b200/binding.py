@@ -27,9 +27,10 @@ BERT_SYMBOLS = ["bert_load_from_file", "bert_free", "bert_encode", "bert_encode_
                 "bert_eval_batch", "bert_n_embd", "bert_n_max_tokens", "bert_vocab_id_to_token", "bert_model_quantize",
                 "bert_params_parse"]
 BK_SYMBOLS = ["bk_device_count", "bk_last_error", "bk_engine_create", "bk_engine_destroy", "bk_engine_set_tensor",
-              "bk_engine_finalize", "bk_engine_forward", "bk_engine_submit", "bk_engine_collect", "bk_engine_stage", "bk_engine_run_staged", "bk_engine_read_output",
+              "bk_engine_finalize", "bk_engine_forward", "bk_engine_submit", "bk_engine_collect", "bk_engine_submit_ragged", "bk_host_alloc", "bk_host_free",
+              "bk_engine_graph_stats", "bk_bert_graph_stats", "bk_engine_stage", "bk_engine_run_staged", "bk_engine_read_output",
               "bk_engine_kernel_ms", "bk_engine_read_hidden", "bk_engine_set_keep_hidden", "bk_engine_launch_count", "bk_profiler_range",
-              "bk_test_gemm", "bk_test_gemm_ln", "bk_test_gelu", "bk_test_add_ln", "bk_test_attention", "bk_test_pool",
+              "bk_test_gemm", "bk_test_gemm_ln", "bk_test_gelu", "bk_test_add_ln", "bk_test_attention", "bk_test_pool", "bk_test_batcher", "bk_test_embed_ln",
               "bk_tokenizer_create", "bk_tokenizer_destroy", "bk_tokenizer_encode"]
 
 
@@ -85,6 +86,16 @@ def load_library(path: str | None = None):
     L.bk_engine_set_tensor.argtypes = [vp, i32, i32, vp, i64, i64]
     L.bk_engine_finalize.argtypes = [vp]
     L.bk_engine_forward.argtypes = [vp, _i32p, _i32p, i32, _f32p]
+    L.bk_engine_submit.argtypes = [vp, i32, _i32p, _i32p, i32]
+    L.bk_engine_collect.argtypes = [vp, i32, _f32p]
+    L.bk_engine_submit_ragged.argtypes = [vp, i32, ctypes.POINTER(_i32p), _i32p, i32, _f32p]
+    L.bk_host_alloc.restype = vp
+    L.bk_host_alloc.argtypes = [ctypes.c_size_t]
+    L.bk_host_free.restype = None
+    L.bk_host_free.argtypes = [vp]
+    _i64p = ctypes.POINTER(ctypes.c_int64)
+    L.bk_engine_graph_stats.argtypes = [vp, _i64p, _i64p, _i64p]
+    L.bk_bert_graph_stats.argtypes = [vp, _i64p, _i64p, _i64p]
     L.bk_engine_stage.argtypes = [vp, _i32p, _i32p, i32]
     L.bk_engine_run_staged.argtypes = [vp, i32, i32, _f32p]
     L.bk_engine_read_output.argtypes = [vp, _f32p, i32]
@@ -100,6 +111,8 @@ def load_library(path: str | None = None):
     L.bk_test_add_ln.argtypes = [ctypes.c_int, i32, i32, ctypes.c_float, _u16p, _f32p, _f32p, i32, _u16p, _u16p]
     L.bk_test_attention.argtypes = [ctypes.c_int, i32, _i32p, i32, i32, _u16p, i32, _u16p]
     L.bk_test_pool.argtypes = [ctypes.c_int, i32, _i32p, i32, _u16p, _f32p]
+    L.bk_test_batcher.argtypes = [ctypes.c_int, i32, _i32p, _i32p, _i32p, _i32p, _i32p, _i32p]
+    L.bk_test_embed_ln.argtypes = [ctypes.c_int, i32, i32, i32, i32, i32, vp, vp, vp, _f32p, _f32p, ctypes.c_float, _i32p, _i32p, i32, _u16p, _u16p]
     L.bk_tokenizer_create.restype = vp
     L.bk_tokenizer_create.argtypes = [ctypes.c_char_p, i64]
     L.bk_tokenizer_destroy.restype = None
@@ -179,6 +192,13 @@ class BertB200:
         toks, tp, lens, op, out = self.make_batch_args(batch)
         self.lib.bert_eval_batch(self.ctx, 1, len(toks), tp, _ptr(lens, _i32p), op)
         return out
+
+    def graph_stats(self) -> dict:
+        """latency path bookkeeping summed over the context's engines: launches replayed from a captured CUDA graph, shapes
+        captured, launches done directly (first sighting of a shape)"""
+        a, b, c = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(0)
+        self.lib.bk_bert_graph_stats(self.ctx, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+        return {"replayed": a.value, "captured": b.value, "direct": c.value}
 
     def tokenize(self, text: str) -> np.ndarray:
         buf = np.zeros(self.n_max_tokens, np.int32)

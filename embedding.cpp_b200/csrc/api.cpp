@@ -3,11 +3,13 @@
 // Host-side replacement of the reference's model layer: bert_loader / bert_load_from_file
 // (bert.cpp:143-659, 783-819), bert_eval / bert_eval_batch (bert.cpp:1020-1108), bert_encode_batch
 // (bert.cpp:1119-1198), bert_tokenize (bert.cpp:738-781).  Where the reference loops over sentences and
-// builds one CPU graph each (bert.cpp:1065), this layer sorts the sentences by length, packs them
-// into token-budget micro-batches and deals those to one engine per GPU (sentences are independent:
-// no collective, host-side gather only).
+// builds one CPU graph each (bert.cpp:1065), this layer cuts the call into token-budget micro-batches
+// and deals those to persistent workers, one per engine / GPU (sentences are independent: no collective,
+// host-side gather only); each micro-batch is sorted by length and packed on the device.
 #include <algorithm>
 #include <atomic>
+#include <condition_variable>
+#include <functional>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -25,6 +27,61 @@
 
 using namespace bk;
 
+// One persistent worker thread per engine (created at load): bert_eval_batch posts a job, the workers run it, the caller waits.
+// Spawning std::threads per call (the first version) cost more than a 128-sentence shard's GPU time at 8 GPUs.
+class WorkerPool {
+  public:
+    explicit WorkerPool(int n) : n_(n) {
+        for (int i = 1; i < n_; i++) th_.emplace_back([this, i] { loop(i); });  // worker 0 is the calling thread
+    }
+    ~WorkerPool() {
+        { std::lock_guard<std::mutex> l(mu_); stop_ = true; }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+    // runs fn(worker) on workers 0..n_active-1 (worker 0 = caller) and returns when all are done
+    void run(int n_active, const std::function<void(int)> &fn) {
+        if (n_active > n_) n_active = n_;
+        if (n_active <= 1) { fn(0); return; }
+        {
+            std::lock_guard<std::mutex> l(mu_);
+            fn_ = &fn; active_ = n_active; pending_ = n_active - 1; gen_++;
+        }
+        cv_.notify_all();
+        fn(0);
+        std::unique_lock<std::mutex> l(mu_);
+        done_.wait(l, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+
+  private:
+    void loop(int id) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)> *fn = nullptr;
+            {
+                std::unique_lock<std::mutex> l(mu_);
+                cv_.wait(l, [&] { return stop_ || gen_ != seen; });
+                if (stop_) return;
+                seen = gen_;
+                if (id < active_) fn = fn_;
+            }
+            if (!fn) continue;
+            (*fn)(id);
+            std::lock_guard<std::mutex> l(mu_);
+            if (--pending_ == 0) done_.notify_one();
+        }
+    }
+    int n_;
+    std::vector<std::thread> th_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)> *fn_ = nullptr;
+    int active_ = 0, pending_ = 0;
+    uint64_t gen_ = 0;
+    bool stop_ = false;
+};
+
 struct bert_ctx {
     GgufFile file;
     bk_hparams hp{};
@@ -35,6 +92,11 @@ struct bert_ctx {
     std::vector<bk_engine *> engines;  // n_gpus distinct devices, engines.size() / n_gpus engines on each
     int n_gpus = 1;
     int cap_tokens = 0, cap_seqs = 0;
+    std::unique_ptr<WorkerPool> pool;
+    // the job's embeddings land here (pinned; every engine's device->host copy targets its own rows) and are handed to the caller's
+    // rows only after every micro-batch succeeded: a failing call leaves the caller's outputs untouched (bert.h:83)
+    float *job_out = nullptr;
+    size_t job_out_rows = 0;
     std::mutex mu;  // one in-flight call per context (the reference is not re-entrant either, bert.cpp:1056-1062)
 };
 
@@ -94,7 +156,7 @@ std::vector<int> pick_devices() {
     return devs;
 }
 
-struct MicroBatch { int begin, end, tokens; };  // range in the length-sorted order
+struct MicroBatch { int begin, end, tokens; };  // sentence range of the job, in the caller's order
 
 }  // namespace
 
@@ -121,15 +183,28 @@ BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
     }
     if (!g.get_f32("bert.attention.layer_norm_epsilon", hp.eps)) { fprintf(stderr, "%s: key not found in model: bert.attention.layer_norm_epsilon\n", __func__); return nullptr; }
     if (hp.n_layer < 1 || hp.n_embd < 1 || hp.n_head < 1 || hp.n_max_tokens < 1) { fprintf(stderr, "%s: invalid hyper-parameters\n", __func__); return nullptr; }
+    if (hp.n_max_tokens > 512) {  // fail at load, not at the first long sentence: the attention kernels hold at most 512 keys per sentence
+        fprintf(stderr, "%s: bert.context_length %d is not supported (maximum 512)\n", __func__, hp.n_max_tokens);
+        return nullptr;
+    }
     // llm_load_tokenizer, bert.cpp:515-578 (special ids optional)
     if (g.get_u32("tokenizer.ggml.cls_token_id", v)) ctx->cls_id = (int32_t)v;
     if (g.get_u32("tokenizer.ggml.seperator_token_id", v)) ctx->sep_id = (int32_t)v;  // (sic) gguf.h:297
     if (g.get_u32("tokenizer.ggml.padding_token_id", v)) ctx->pad_id = (int32_t)v;
     if (g.get_u32("tokenizer.ggml.unknown_token_id", v)) ctx->unk_id = (int32_t)v;
-    if (const GgufValue *blob = g.find("blob.tokenizer.json")) {
-        std::string terr;
-        ctx->tok_ok = ctx->tok.load(blob->s, terr);
-        if (!ctx->tok_ok) fprintf(stderr, "%s: warning: tokenizer.json not usable (%s); bert_tokenize/bert_encode disabled\n", __func__, terr.c_str());
+    // blob.tokenizer.json is a required key in the reference (bert.cpp:576), and a tokenizer that cannot be built must not turn every
+    // text into [CLS][SEP] silently.  BERT_B200_ALLOW_NO_TOKENIZER=1 opts in to an ids-only context (bert_eval / bert_eval_batch work,
+    // bert_tokenize / bert_encode* report an error and leave their outputs untouched).
+    {
+        const bool allow = env_int("BERT_B200_ALLOW_NO_TOKENIZER", 0) != 0;
+        const GgufValue *blob = g.find("blob.tokenizer.json");
+        std::string terr = "key not found in model: blob.tokenizer.json";
+        if (blob) ctx->tok_ok = ctx->tok.load(blob->s, terr);
+        if (!ctx->tok_ok) {
+            fprintf(stderr, "%s: %s tokenizer not usable (%s)%s\n", __func__, allow ? "warning:" : "error:", terr.c_str(),
+                    allow ? "; bert_tokenize / bert_encode disabled" : " -- set BERT_B200_ALLOW_NO_TOKENIZER=1 to load for bert_eval only");
+            if (!allow) return nullptr;
+        }
     }
     // file type = most frequent tensor type among 2-D tensors (bert.cpp:206-252 counts all tensors; the
     // 2-D ones decide which GEMM path is used and are what the converter/quantiser change)
@@ -139,6 +214,7 @@ BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
         const GgufTensor *t = g.tensor(nm);
         if (!t) { fprintf(stderr, "%s: tensor '%s' not found\n", __func__, nm.c_str()); return nullptr; }
         if (t->type > 3 || t->nbytes == 0) { fprintf(stderr, "%s: tensor '%s' has unsupported type %u (supported: F32, F16, Q4_0, Q4_1)\n", __func__, nm.c_str(), t->type); return nullptr; }
+        if (t->n_dims > 2 || t->ne[2] != 1 || t->ne[3] != 1) { fprintf(stderr, "%s: tensor '%s' has more than 2 dimensions\n", __func__, nm.c_str()); return nullptr; }
         if (t->n_dims == 2) cnt[t->type]++;
     }
     hp.wtype = (int32_t)(std::max_element(cnt, cnt + 4) - cnt);
@@ -164,6 +240,7 @@ BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
         }
         if (bk_engine_finalize(e) != 0) { fprintf(stderr, "%s: %s\n", __func__, bk_last_error()); bert_free(ctx.release()); return nullptr; }
     }
+    ctx->pool.reset(new WorkerPool((int)ctx->engines.size()));
     if (env_int("BERT_B200_VERBOSE", 0))
         fprintf(stderr, "%s: %s: d=%d f=%d heads=%d layers=%d vocab=%d wtype=%d on %d GPU(s), %zu engine(s), micro-batch %d tokens\n", __func__, fname,
                 hp.n_embd, hp.n_intermediate, hp.n_head, hp.n_layer, hp.n_vocab, hp.wtype, ctx->n_gpus, ctx->engines.size(), ctx->cap_tokens);
@@ -172,7 +249,9 @@ BERT_API struct bert_ctx *bert_load_from_file(const char *fname) {
 
 BERT_API void bert_free(struct bert_ctx *ctx) {
     if (!ctx) return;
+    ctx->pool.reset();
     for (bk_engine *e : ctx->engines) bk_engine_destroy(e);
+    bk_host_free(ctx->job_out);
     delete ctx;
 }
 
@@ -181,6 +260,61 @@ BERT_API int32_t bert_n_max_tokens(struct bert_ctx *ctx) { return ctx->hp.n_max_
 BERT_API const char *bert_vocab_id_to_token(struct bert_ctx *ctx, bert_vocab_id id) {
     if (id < 0 || id >= (int32_t)ctx->vocab.size()) return nullptr;
     return ctx->vocab[id].c_str();
+}
+
+// sentences [b0, b0 + n) of the caller's arrays: micro-batches cut in the caller's order by token budget, dealt to the engines; the
+// embeddings land in ctx->job_out (row i = sentence b0 + i).  Sorting by length, packing and the return to the caller's order happen on
+// the device (on-device batcher, rowwise.cu).  Returns false if any engine failed.
+static bool run_job(bert_ctx *ctx, int b0, int n, bert_vocab_id **batch_tokens, const int32_t *n_tokens) {
+    const int N = ctx->hp.n_max_tokens, d = ctx->hp.n_embd;
+    long long total = 0;
+    for (int b = 0; b < n; b++) total += n_tokens[b0 + b];
+    const int n_eng = (int)ctx->engines.size();
+    long long budget = ctx->cap_tokens;
+    // several GPUs: one share per GPU (a GPU's second engine only takes work when its share exceeds a micro-batch)
+    if (ctx->n_gpus > 1) budget = std::min<long long>(budget, std::max<long long>((total + ctx->n_gpus - 1) / ctx->n_gpus, N));
+    std::vector<MicroBatch> mbs;
+    for (int i = 0; i < n;) {
+        int j = i, t = 0;
+        while (j < n && j - i < ctx->cap_seqs && t + n_tokens[b0 + j] <= budget) { t += n_tokens[b0 + j]; j++; }
+        mbs.push_back({i, j, t});
+        i = j;
+    }
+    std::atomic<int> next{0};
+    std::atomic<int> failed{0};
+    const std::function<void(int)> worker = [&](int ei) {
+        // two micro-batches in flight per engine: while batch k runs on the GPU, batch k+1 is staged, uploaded and enqueued
+        bk_engine *e = ctx->engines[ei];
+        bool pending[2] = {false, false};
+        auto wait_slot = [&](int slot) -> bool {
+            if (!pending[slot]) return true;
+            pending[slot] = false;
+            if (bk_engine_collect(e, slot, nullptr) != 0) {
+                fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error());
+                failed.store(1);
+                return false;
+            }
+            return true;
+        };
+        for (int k = 0;; k++) {
+            const int slot = k & 1;
+            const int m = next.fetch_add(1);
+            if (m >= (int)mbs.size() || failed.load()) break;
+            if (!wait_slot(slot)) break;  // the slot's previous batch (k-2) must have left its staging buffers
+            const MicroBatch &mb = mbs[m];
+            if (bk_engine_submit_ragged(e, slot, batch_tokens + b0 + mb.begin, n_tokens + b0 + mb.begin, mb.end - mb.begin,
+                                        ctx->job_out + (size_t)mb.begin * d) != 0) {
+                fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error());
+                failed.store(1);
+                break;
+            }
+            pending[slot] = true;
+        }
+        wait_slot(0);
+        wait_slot(1);
+    };
+    ctx->pool->run(std::min<int>(n_eng, (int)mbs.size()), worker);
+    return failed.load() == 0;
 }
 
 BERT_API void bert_eval_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n_batch_size, bert_vocab_id **batch_tokens,
@@ -194,80 +328,28 @@ BERT_API void bert_eval_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n
         if (n_tokens[b] < 1) { fprintf(stderr, "Empty input %d: at least one token is required\n", b); return; }
     }
     std::lock_guard<std::mutex> lock(ctx->mu);
-    // length-sorted order (longest first), then token-budget micro-batches
-    std::vector<int> order(n_batch_size);
-    std::iota(order.begin(), order.end(), 0);
-    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return n_tokens[a] > n_tokens[b]; });
-    long long total = 0;
-    for (int b = 0; b < n_batch_size; b++) total += n_tokens[b];
-    const int n_eng = (int)ctx->engines.size();
-    long long budget = ctx->cap_tokens;
-    // several GPUs: one share per GPU (a GPU's second engine only takes work when its share exceeds a micro-batch)
-    if (ctx->n_gpus > 1) budget = std::min<long long>(budget, std::max<long long>((total + ctx->n_gpus - 1) / ctx->n_gpus, N));
-    std::vector<MicroBatch> mbs;
-    for (int i = 0; i < n_batch_size;) {
-        int j = i, t = 0;
-        while (j < n_batch_size && j - i < ctx->cap_seqs && t + n_tokens[order[j]] <= budget) { t += n_tokens[order[j]]; j++; }
-        mbs.push_back({i, j, t});
-        i = j;
+    // jobs of at most kJobRows sentences (bounds the pinned result buffer); the all-or-nothing guarantee is per job
+    const int kJobRows = 1 << 18;
+    const size_t want = (size_t)std::min(n_batch_size, kJobRows);
+    if (ctx->job_out_rows < want) {
+        bk_host_free(ctx->job_out);
+        ctx->job_out_rows = 0;
+        size_t rows = 1024;
+        while (rows < want) rows *= 2;
+        ctx->job_out = (float *)bk_host_alloc(rows * (size_t)d * sizeof(float));
+        if (!ctx->job_out) { fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error()); return; }
+        ctx->job_out_rows = rows;
     }
-    std::atomic<int> next{0};
-    std::atomic<int> failed{0};
-    auto worker = [&](int ei) {
-        // two micro-batches in flight per engine: while batch k runs on the GPU, batch k+1 is packed, uploaded and
-        // enqueued, and batch k-1's embeddings are scattered to the caller's rows
-        bk_engine *e = ctx->engines[ei];
-        std::vector<int32_t> toks, lens;
-        std::vector<float> out;
-        int pending_mb[2] = {-1, -1};
-        auto collect = [&](int slot) -> bool {
-            const int m = pending_mb[slot];
-            if (m < 0) return true;
-            pending_mb[slot] = -1;
-            const MicroBatch &mb = mbs[m];
-            const int ns = mb.end - mb.begin;
-            out.resize((size_t)ns * d);
-            if (bk_engine_collect(e, slot, out.data()) != 0) {
-                fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error());
-                failed.store(1);
-                return false;
-            }
-            for (int s = 0; s < ns; s++) memcpy(batch_embeddings[order[mb.begin + s]], out.data() + (size_t)s * d, (size_t)d * sizeof(float));
-            return true;
+    for (int b0 = 0; b0 < n_batch_size; b0 += kJobRows) {
+        const int n = std::min(kJobRows, n_batch_size - b0);
+        if (!run_job(ctx, b0, n, batch_tokens, n_tokens)) return;  // outputs of this job untouched
+        // hand the rows to the caller (the only host pass over the embeddings); large jobs: spread over the workers
+        const std::function<void(int)> scatter = [&](int w) {
+            const int nw = std::min<int>((int)ctx->engines.size(), std::max(1, n / 2048));
+            for (int i = (int)((long long)n * w / nw), hi = (int)((long long)n * (w + 1) / nw); i < hi; i++)
+                memcpy(batch_embeddings[b0 + i], ctx->job_out + (size_t)i * d, (size_t)d * sizeof(float));
         };
-        for (int k = 0;; k++) {
-            const int slot = k & 1;
-            const int m = next.fetch_add(1);
-            if (m >= (int)mbs.size() || failed.load()) break;
-            if (!collect(slot)) break;   // the slot's previous batch (k-2) must be read back before its buffers are reused
-            const MicroBatch &mb = mbs[m];
-            const int ns = mb.end - mb.begin;
-            toks.resize(mb.tokens); lens.resize(ns);
-            int off = 0;
-            for (int s = 0; s < ns; s++) {
-                const int b = order[mb.begin + s];
-                lens[s] = n_tokens[b];
-                memcpy(toks.data() + off, batch_tokens[b], (size_t)n_tokens[b] * sizeof(int32_t));
-                off += n_tokens[b];
-            }
-            if (bk_engine_submit(e, slot, toks.data(), lens.data(), ns) != 0) {
-                fprintf(stderr, "bert_eval_batch: %s\n", bk_last_error());
-                failed.store(1);
-                break;
-            }
-            pending_mb[slot] = m;
-            if (!collect(slot ^ 1)) break;  // batch k-1: overlaps with batch k on the GPU
-        }
-        collect(0);
-        collect(1);
-    };
-    const int n_workers = std::min<int>(n_eng, (int)mbs.size());
-    if (n_workers <= 1) worker(0);
-    else {
-        std::vector<std::thread> th;
-        for (int i = 1; i < n_workers; i++) th.emplace_back(worker, i);
-        worker(0);
-        for (auto &t : th) t.join();
+        ctx->pool->run(std::min<int>((int)ctx->engines.size(), std::max(1, n / 2048)), scatter);
     }
 }
 
@@ -279,8 +361,8 @@ BERT_API void bert_tokenize(struct bert_ctx *ctx, const char *text, bert_vocab_i
     // bert.cpp:738-781: [CLS] + ids (stop at the first PAD id or when full) + [SEP]; when full the last slot is SEP
     *n_tokens = 0;
     if (n_max_tokens < 2) return;
-    std::vector<int32_t> ids;
-    if (ctx->tok_ok) ids = ctx->tok.encode(text ? text : "");
+    if (!ctx->tok_ok) { fprintf(stderr, "bert_tokenize: this context was loaded without a usable tokenizer\n"); return; }
+    const std::vector<int32_t> ids = ctx->tok.encode(text ? text : "");
     int t = 0;
     tokens[t++] = ctx->cls_id;
     for (int32_t id : ids) {
@@ -297,6 +379,7 @@ BERT_API void bert_encode_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t
                                 float **embeddings) {
     (void)n_batch_size;  // the reference overrides it to 1 (bert.cpp:1128); here the whole call is one sorted batch
     if (!ctx || n_inputs <= 0) return;
+    if (!ctx->tok_ok) { fprintf(stderr, "bert_encode_batch: this context was loaded without a usable tokenizer; outputs untouched\n"); return; }
     const int N = ctx->hp.n_max_tokens;
     std::vector<int32_t> buf((size_t)n_inputs * N);
     std::vector<int32_t *> ptrs(n_inputs);
@@ -328,6 +411,19 @@ BERT_API void bert_encode(struct bert_ctx *ctx, int32_t n_threads, const char *t
 
 struct bk_tokenizer { WordPieceTokenizer tok; };
 extern "C" {
+BK_API int bk_bert_graph_stats(struct bert_ctx *ctx, int64_t *replayed, int64_t *captured, int64_t *direct) {
+    if (!ctx) return -1;
+    int64_t r = 0, c = 0, d = 0;
+    for (bk_engine *e : ctx->engines) {
+        int64_t a = 0, b = 0, x = 0;
+        bk_engine_graph_stats(e, &a, &b, &x);
+        r += a; c += b; d += x;
+    }
+    if (replayed) *replayed = r;
+    if (captured) *captured = c;
+    if (direct) *direct = d;
+    return 0;
+}
 BK_API bk_tokenizer *bk_tokenizer_create(const char *json, int64_t json_len) {
     std::unique_ptr<bk_tokenizer> t(new bk_tokenizer());
     std::string err;

@@ -3,7 +3,7 @@
 //
 // Replaces bert_build + ggml_graph_compute_with_ctx (bert.cpp:845-1012, 1077-1099; ggml.c:15961-16049):
 // the reference builds and walks a ~45-node-per-layer graph per sentence on CPU threads; here the plan
-// is static -- 2 + 7*n_layer + 2 kernel launches per batch on one CUDA stream.
+// is static -- 2 (on-device batcher) + 1 + 7*n_layer + 1 kernel launches per batch on one CUDA stream.
 //
 // HBM layout (T = packed tokens of the launch, d = n_embd, f = n_intermediate; all activations f16):
 //   x   [T][d]   residual stream / LN output        xq  [T][d]  its Q8-rounded copy (Q4 models only)
@@ -94,6 +94,9 @@ struct bk_engine {
     cudaEvent_t slot_done[2] = {nullptr, nullptr};
     int slot_nseq[2] = {0, 0};
     int32_t *d_cu = nullptr, *d_pos = nullptr;
+    // on-device batcher (rowwise.cu): packed, length-sorted ids; sorted position -> caller index; scratch
+    int32_t *d_tok = nullptr, *d_order = nullptr, *d_src_off = nullptr, *d_caller_off = nullptr;
+    float *slot_host_out[2] = {nullptr, nullptr};  // where slot's embeddings were copied to (caller's pinned buffer or h_out2)
     __half *x = nullptr, *xq = nullptr, *qkv = nullptr, *att = nullptr, *pre = nullptr, *y = nullptr, *yq = nullptr, *h = nullptr;
     CUtensorMap tm_x, tm_att, tm_y, tm_h;  // A-operand maps (x/y point at the Q8-rounded copy for Q4 models)
     CUtensorMap to_qkv, to_pre, to_h;      // GEMM output maps (TMA stores), box {64, 128}
@@ -104,7 +107,7 @@ struct bk_engine {
     // staged batch
     int st_T = 0, st_nseq = 0, st_maxlen = 0;  // last forward (hidden-state readback)
     // staged set (bench `value` leg): a whole job resident in HBM, cut into micro-batches of <= cap_tokens
-    // n_long / max_short: the sentences of more than 128 tokens form the first n_long of the slice (length-sorted input) and the
+    // n_long / max_short: the slice has n_long sentences of more than 128 tokens (the on-device batcher puts them first) and the
     // longest of the others has max_short tokens -> attention runs as two launches, each with the kernel made for its lengths;
     // n_long = 0: one launch for all
     struct Slice { int tok_off, seq_off, T, n_seq, max_len, n_long, max_short; };
@@ -117,10 +120,17 @@ struct bk_engine {
     bool keep_hidden = false;
     __half *hidden = nullptr;  // [n_layer+1][cap_tokens][d]
     // CUDA graphs of the launch plan for small batches (latency path): key = (T, n_seq, max_len)
-    struct GraphEntry { int T, n_seq, max_len, n_long, max_short, slot; cudaGraphExec_t exec; uint64_t last_use; };
+    struct GraphKey {
+        int T, n_seq, max_len, n_long, max_short, slot;
+        bool operator==(const GraphKey &o) const { return T == o.T && n_seq == o.n_seq && max_len == o.max_len && n_long == o.n_long && max_short == o.max_short && slot == o.slot; }
+    };
+    struct GraphEntry { GraphKey key; cudaGraphExec_t exec; uint64_t last_use; };
     std::vector<GraphEntry> graphs;
+    std::vector<GraphKey> seen_once;  // shapes launched directly once; the second sighting captures (ring, newest last)
     uint64_t graph_clock = 0;
     int graph_max_tokens = 4096;  // BERT_B200_GRAPH_TOKENS; 0 disables
+    int graph_cache = 1024;       // BERT_B200_GRAPH_CACHE: captured shapes kept (least recently used is evicted)
+    int64_t graph_hits = 0, graph_captures = 0, graph_direct = 0;
     // Q4 models: batches of up to this many tokens (the latency regime) run the GEMMs from the packed weights (decoded in shared memory,
     // only Q4 bytes cross HBM: weight traffic dominates there); larger ones use the f16 operand copies, where
     // weights are < 2% of the bytes moved and the decode would compete with the epilogue for issue slots.
@@ -162,7 +172,11 @@ static int engine_alloc(bk_engine *e) {
         CK(cudaEventCreateWithFlags(&e->slot_done[sl], cudaEventDisableTiming));
     }
     CK(cudaMalloc(&e->d_pos, T * 4));
+    CK(cudaMalloc(&e->d_tok, T * 4));
     CK(cudaMalloc(&e->d_cu, ((size_t)e->cap_seqs + 1) * 4));
+    CK(cudaMalloc(&e->d_order, (size_t)e->cap_seqs * 4));
+    CK(cudaMalloc(&e->d_src_off, (size_t)e->cap_seqs * 4));
+    CK(cudaMalloc(&e->d_caller_off, (size_t)e->cap_seqs * 4));
     CK(cudaMalloc(&e->x, T * d * 2));
     CK(cudaMalloc(&e->qkv, T * 3 * d * 2));
     CK(cudaMalloc(&e->att, T * d * 2));
@@ -195,6 +209,8 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     if (dh != 32 && dh != 64) { fail("unsupported head size %d (supported: 32, 64)", dh); return nullptr; }
     if (hp->n_embd > 2048) { fail("unsupported n_embd %d (> 2048)", hp->n_embd); return nullptr; }
     if (hp->wtype < BK_F32 || hp->wtype > BK_Q4_1) { fail("unsupported weight type %d", hp->wtype); return nullptr; }
+    // the attention kernels hold one sentence's keys on chip: 512 tokens at most (every BERT checkpoint's context length)
+    if (hp->n_max_tokens < 1 || hp->n_max_tokens > 512) { fail("unsupported context length %d (supported: 1..512)", hp->n_max_tokens); return nullptr; }
     if (cap_tokens < hp->n_max_tokens) cap_tokens = hp->n_max_tokens;
     cap_tokens = (cap_tokens + 255) & ~255;  // whole CTA-pair tiles (256 rows): stores past T stay inside the buffers
     if (cap_seqs < 1) cap_seqs = 1;
@@ -210,6 +226,7 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     e->num_sms = prop.multiProcessorCount;
     e->qmode = hp->wtype == BK_Q4_0 ? 1 : hp->wtype == BK_Q4_1 ? 2 : 0;
     if (const char *v = getenv("BERT_B200_GRAPH_TOKENS")) e->graph_max_tokens = atoi(v);
+    if (const char *v = getenv("BERT_B200_GRAPH_CACHE")) e->graph_cache = atoi(v) > 0 ? atoi(v) : 1;
     if (const char *v = getenv("BERT_B200_Q4_SMEM_TOKENS")) e->q4_smem_tokens = atoi(v);
     if (const char *v = getenv("BERT_B200_FUSED_LN_TOKENS")) e->fused_ln_tokens = atoi(v);
     e->tens.resize(5 + 16 * (size_t)hp->n_layer);
@@ -228,7 +245,8 @@ BK_API void bk_engine_destroy(bk_engine *e) {
         cudaFree(l.wqkv); cudaFree(l.wo); cudaFree(l.w1); cudaFree(l.w2); cudaFree(l.bqkv);
         cudaFree(l.pqkv); cudaFree(l.po); cudaFree(l.p1); cudaFree(l.p2);
     }
-    void *bufs[] = {e->d_tokens2[0], e->d_tokens2[1], e->d_lens2[0], e->d_lens2[1], e->d_out2[0], e->d_out2[1], e->d_cu, e->d_pos, e->x, e->xq, e->qkv,
+    void *bufs[] = {e->d_tokens2[0], e->d_tokens2[1], e->d_lens2[0], e->d_lens2[1], e->d_out2[0], e->d_out2[1], e->d_cu, e->d_pos, e->d_tok, e->d_order,
+                    e->d_src_off, e->d_caller_off, e->x, e->xq, e->qkv,
                     e->att, e->pre, e->y, e->yq, e->h, e->hidden, e->sg_tokens, e->sg_lens, e->sg_out};
     for (void *b : bufs) if (b) cudaFree(b);
     for (int sl = 0; sl < 2; sl++) {
@@ -401,9 +419,10 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
     const bk_hparams &hp = e->hp;
     const int d = hp.n_embd, f = hp.n_intermediate;
     const int q = e->qmode;
-    {
+    {   // on-device batcher: sort the sentences by length, pack them, positions; d_tokens / d_lens are in the caller's order
         KTimer t(e, BK_K_PACK);
-        CK(launch_pack(d_lens, n_seq, e->d_cu, e->d_pos, T, e->st));
+        BatcherParams b{d_tokens, d_lens, n_seq, T, e->d_tok, e->d_pos, e->d_cu, e->d_order, e->d_src_off, e->d_caller_off};
+        CK(launch_batcher(b, e->st));
         e->launch_count += 2;
     }
     {
@@ -411,7 +430,7 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
         EmbedParams p;
         p.word = e->tens[0].dev; p.type = e->tens[1].dev; p.posw = e->tens[2].dev; p.wtype = e->tens[0].type;
         p.gamma = (const float *)e->tens[3].dev; p.beta = (const float *)e->tens[4].dev;
-        p.tokens = d_tokens; p.pos = e->d_pos; p.T = T; p.d = d; p.n_vocab = hp.n_vocab; p.eps = hp.eps;
+        p.tokens = e->d_tok; p.pos = e->d_pos; p.T = T; p.d = d; p.n_vocab = hp.n_vocab; p.eps = hp.eps;
         p.x = e->x; p.xq = e->xq; p.qmode = q;
         CK(launch_embed_ln(p, e->st));
         e->launch_count++;
@@ -459,31 +478,40 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
     }
     {
         KTimer t(e, BK_K_POOL);
-        CK(launch_pool_norm(e->x, e->d_cu, n_seq, d, d_out, e->st));
+        CK(launch_pool_norm(e->x, e->d_cu, e->d_order, n_seq, d, d_out, e->st));  // row order[s]: the caller's order
         e->launch_count++;
     }
     return 0;
 }
 
-// the same launch sequence captured once per (T, n_seq, max_len) and replayed (kernel arguments -- sizes, tensor
-// maps, engine-owned device pointers -- are identical for equal keys); least-recently-used of 32 shapes is evicted
+// Small batches (the latency path): the launch sequence is captured per shape key and replayed as a CUDA graph (kernel arguments --
+// sizes, tensor maps, engine-owned device pointers -- are identical for equal keys).  A shape is launched DIRECTLY the first time it
+// is seen and captured only when it comes back (capture + instantiation of 4 + 7L nodes costs several direct passes; traffic with
+// ever-new shapes must not pay it per call).  Direct small-batch launches use programmatic dependent launch like the captured plan.
+// Returns 1 = ran as a graph, 0 = caller must launch directly, < 0 error.
 int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, int n_long, int max_short) {
     e->graph_clock++;
+    const bk_engine::GraphKey key{T, n_seq, max_len, n_long, max_short, slot};
     for (auto &g : e->graphs)
-        if (g.T == T && g.n_seq == n_seq && g.max_len == max_len && g.n_long == n_long && g.max_short == max_short && g.slot == slot) {
+        if (g.key == key) {
             g.last_use = e->graph_clock;
             CK(cudaGraphLaunch(g.exec, e->st));
             e->launch_count += 4 + 7 * e->hp.n_layer;
-            return 0;
+            e->graph_hits++;
+            return 1;
         }
+    bool second = false;
+    for (size_t i = 0; i < e->seen_once.size(); i++)
+        if (e->seen_once[i] == key) { e->seen_once.erase(e->seen_once.begin() + (long)i); second = true; break; }
+    if (!second) {
+        if (e->seen_once.size() >= 4096) e->seen_once.erase(e->seen_once.begin());
+        e->seen_once.push_back(key);
+        e->graph_direct++;
+        return 0;
+    }
     cudaGraph_t graph = nullptr;
     CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
-    // the latency path: kernel boundaries become programmatic dependencies, so every kernel's set-up (and its launch) runs
-    // under the tail of the one before it (common.cuh: pdl_wait).  BERT_B200_PDL=0 captures plain edges.
-    static const bool use_pdl = [] { const char *v = getenv("BERT_B200_PDL"); return !v || atoi(v) != 0; }();
-    pdl_flag() = use_pdl;
     const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, max_len, n_long, max_short, e->d_out2[slot]);
-    pdl_flag() = false;
     const cudaError_t ce = cudaStreamEndCapture(e->st, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (ce != cudaSuccess) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(ce));
@@ -491,25 +519,26 @@ int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, int n_l
     const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
     cudaGraphDestroy(graph);
     if (ie != cudaSuccess) return fail("cudaGraphInstantiate: %s", cudaGetErrorString(ie));
-    if (e->graphs.size() >= 32) {
+    if ((int)e->graphs.size() >= e->graph_cache) {
         size_t lru = 0;
         for (size_t i = 1; i < e->graphs.size(); i++) if (e->graphs[i].last_use < e->graphs[lru].last_use) lru = i;
         cudaGraphExecDestroy(e->graphs[lru].exec);
         e->graphs.erase(e->graphs.begin() + (long)lru);
     }
-    e->graphs.push_back({T, n_seq, max_len, n_long, max_short, slot, exec, e->graph_clock});
+    e->graphs.push_back({key, exec, e->graph_clock});
+    e->graph_captures++;
     CK(cudaGraphLaunch(exec, e->st));
-    return 0;
+    return 1;
 }
 
-// sentences of more than 128 tokens first?  -> their count and the longest of the rest; otherwise (or when there are none, or
-// nothing else) n_long = 0
+// the batcher sorts by length on the device, so the sentences of more than 128 tokens form a prefix of the packed batch whatever the
+// caller's order: their count and the longest of the rest (attention runs as two launches, each with the kernel made for its
+// lengths).  All long, or none: n_long = 0, one launch.
 void split_by_length(const int32_t *lens, int n_seq, int *n_long, int *max_short) {
     int nl = 0, ms = 0;
-    while (nl < n_seq && lens[nl] > 128) nl++;
-    for (int i = nl; i < n_seq; i++) {
-        if (lens[i] > 128) { *n_long = 0; *max_short = 0; return; }  // not sorted: one launch
-        if (lens[i] > ms) ms = lens[i];
+    for (int i = 0; i < n_seq; i++) {
+        if (lens[i] > 128) nl++;
+        else if (lens[i] > ms) ms = lens[i];
     }
     if (nl == n_seq) nl = 0;
     *n_long = nl;
@@ -540,7 +569,7 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
     if (!e || !e->finalized) return fail("engine not finalized");
     if (n_seq < 1) return fail("n_seq %d < 1", n_seq);
     CK(cudaSetDevice(e->device));
-    // cut the job into micro-batches in the given order (callers sort by length, as bert_eval_batch does)
+    // cut the job into micro-batches in the caller's order; each one is sorted by length and packed on the device (rowwise.cu)
     e->slices.clear();
     long long total = 0;
     for (int i = 0; i < n_seq;) {
@@ -571,6 +600,35 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
     return 0;
 }
 
+// ids and lengths of the batch are in the slot's pinned staging buffers: upload, all kernels, download into host_out (pinned, or
+// the slot's own buffer when null)
+static int enqueue_slot(bk_engine *e, int slot, int T, int n_seq, int mx, float *host_out) {
+    const int32_t *lens = e->h_lens2[slot];
+    CK(cudaMemcpyAsync(e->d_tokens2[slot], e->h_tokens2[slot], (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
+    CK(cudaMemcpyAsync(e->d_lens2[slot], e->h_lens2[slot], (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
+    e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
+    int n_long = 0, max_short = 0;
+    split_by_length(lens, n_seq, &n_long, &max_short);
+    const bool small = T <= e->graph_max_tokens && !e->keep_hidden && !e->timing;
+    // the latency path: kernel boundaries are programmatic dependencies, so every kernel's set-up (and its launch) runs under the
+    // tail of the one before it (common.cuh: pdl_wait) -- in the captured plan and in direct launches.  BERT_B200_PDL=0: plain edges.
+    static const bool use_pdl = [] { const char *v = getenv("BERT_B200_PDL"); return !v || atoi(v) != 0; }();
+    int ran = 0;
+    if (small) {
+        pdl_flag() = use_pdl;
+        ran = forward_graph(e, slot, T, n_seq, mx, n_long, max_short);
+        if (ran == 0) ran = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot]) ? -1 : 1;
+        pdl_flag() = false;
+        if (ran < 0) return -1;
+    } else if (forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot])) return -1;
+    float *dst = host_out ? host_out : e->h_out2[slot];
+    CK(cudaMemcpyAsync(dst, e->d_out2[slot], (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaEventRecord(e->slot_done[slot], e->st));
+    e->slot_nseq[slot] = n_seq;
+    e->slot_host_out[slot] = dst;
+    return 0;
+}
+
 BK_API int bk_engine_submit(bk_engine *e, int32_t slot, const int32_t *tokens, const int32_t *lens, int32_t n_seq) {
     int T, mx;
     if (slot < 0 || slot > 1) return fail("slot %d outside 0..1", slot);
@@ -578,27 +636,45 @@ BK_API int bk_engine_submit(bk_engine *e, int32_t slot, const int32_t *tokens, c
     CK(cudaSetDevice(e->device));
     memcpy(e->h_tokens2[slot], tokens, (size_t)T * 4);
     memcpy(e->h_lens2[slot], lens, (size_t)n_seq * 4);
-    CK(cudaMemcpyAsync(e->d_tokens2[slot], e->h_tokens2[slot], (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
-    CK(cudaMemcpyAsync(e->d_lens2[slot], e->h_lens2[slot], (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
-    e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
-    int n_long = 0, max_short = 0;
-    split_by_length(lens, n_seq, &n_long, &max_short);
-    if (T <= e->graph_max_tokens && !e->keep_hidden && !e->timing) {
-        // small batch: the 3 + 7*n_layer + 1 launches cost more host time than GPU time -> replay a captured graph
-        if (forward_graph(e, slot, T, n_seq, mx, n_long, max_short)) return -1;
-    } else if (forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot])) return -1;
-    CK(cudaMemcpyAsync(e->h_out2[slot], e->d_out2[slot], (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
-    CK(cudaEventRecord(e->slot_done[slot], e->st));
-    e->slot_nseq[slot] = n_seq;
-    return 0;
+    return enqueue_slot(e, slot, T, n_seq, mx, nullptr);
+}
+
+BK_API int bk_engine_submit_ragged(bk_engine *e, int32_t slot, const int32_t *const *sent_tokens, const int32_t *sent_lens, int32_t n_seq,
+                                   float *host_out) {
+    int T, mx;
+    if (slot < 0 || slot > 1) return fail("slot %d outside 0..1", slot);
+    if (check_batch(e, sent_lens, n_seq, &T, &mx)) return -1;
+    CK(cudaSetDevice(e->device));
+    int32_t *dst = e->h_tokens2[slot];
+    for (int i = 0; i < n_seq; i++) {  // the only host pass over the ids: caller's rows -> pinned staging, in the caller's order
+        memcpy(dst, sent_tokens[i], (size_t)sent_lens[i] * 4);
+        dst += sent_lens[i];
+    }
+    memcpy(e->h_lens2[slot], sent_lens, (size_t)n_seq * 4);
+    return enqueue_slot(e, slot, T, n_seq, mx, host_out);
 }
 
 BK_API int bk_engine_collect(bk_engine *e, int32_t slot, float *out) {
     if (!e || slot < 0 || slot > 1 || e->slot_nseq[slot] <= 0) return fail("nothing submitted in slot %d", slot);
     CK(cudaSetDevice(e->device));
     CK(cudaEventSynchronize(e->slot_done[slot]));
-    memcpy(out, e->h_out2[slot], (size_t)e->slot_nseq[slot] * e->hp.n_embd * 4);
+    if (out && out != e->slot_host_out[slot]) memcpy(out, e->slot_host_out[slot], (size_t)e->slot_nseq[slot] * e->hp.n_embd * 4);
     e->slot_nseq[slot] = 0;
+    return 0;
+}
+
+BK_API void *bk_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 16, cudaHostAllocPortable) != cudaSuccess) { fail("cudaHostAlloc(%zu) failed", bytes); cudaGetLastError(); return nullptr; }
+    return p;
+}
+BK_API void bk_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+BK_API int bk_engine_graph_stats(bk_engine *e, int64_t *replayed, int64_t *captured, int64_t *direct) {
+    if (!e) return fail("null engine");
+    if (replayed) *replayed = e->graph_hits;
+    if (captured) *captured = e->graph_captures;
+    if (direct) *direct = e->graph_direct;
     return 0;
 }
 

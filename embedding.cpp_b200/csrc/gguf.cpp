@@ -11,13 +11,17 @@
 
 namespace bk {
 
+// sizes come from an untrusted file: every product is overflow-checked (0 = unsupported / implausible, rejected by the loader)
 size_t ggml_tensor_bytes(uint32_t type, const uint64_t ne[4]) {
-    const uint64_t n = ne[0] * ne[1] * ne[2] * ne[3];
+    uint64_t n = 1;
+    for (int i = 0; i < 4; i++)
+        if (__builtin_mul_overflow(n, ne[i], &n)) return 0;
+    uint64_t bytes = 0;
     switch (type) {
-        case 0: return n * 4;                       // F32
-        case 1: return n * 2;                       // F16
-        case 2: return ne[0] % 32 ? 0 : n / 32 * 18;  // Q4_0: f16 d + 16 B
-        case 3: return ne[0] % 32 ? 0 : n / 32 * 20;  // Q4_1: f16 d + f16 m + 16 B
+        case 0: if (__builtin_mul_overflow(n, (uint64_t)4, &bytes)) return 0; return (size_t)bytes;   // F32
+        case 1: if (__builtin_mul_overflow(n, (uint64_t)2, &bytes)) return 0; return (size_t)bytes;   // F16
+        case 2: if (ne[0] % 32 || __builtin_mul_overflow(n / 32, (uint64_t)18, &bytes)) return 0; return (size_t)bytes;  // Q4_0: f16 d + 16 B
+        case 3: if (ne[0] % 32 || __builtin_mul_overflow(n / 32, (uint64_t)20, &bytes)) return 0; return (size_t)bytes;  // Q4_1: f16 d + f16 m + 16 B
     }
     return 0;
 }
@@ -131,10 +135,13 @@ bool GgufFile::open(const char *path, std::string &err) {
         tensors.push_back(std::move(t));
     }
     if (!c.ok) { err = "truncated GGUF tensor-info section"; return false; }
+    if (alignment > (1u << 20) || (alignment & (alignment - 1))) { err = "implausible general.alignment"; return false; }
     data_off = (c.pos + alignment - 1) / alignment * alignment;
+    if (data_off > size) { err = "truncated GGUF file (no data section)"; return false; }
+    const uint64_t room = size - data_off;
     for (const auto &t : tensors) {
         if (t.nbytes == 0) continue;  // unsupported type: reported by the model loader if the tensor is needed
-        if (data_off + t.offset + t.nbytes > size) { err = "tensor " + t.name + " extends past end of file"; return false; }
+        if (t.offset > room || t.nbytes > room - t.offset) { err = "tensor " + t.name + " extends past end of file"; return false; }  // no wrap-around
     }
     return true;
 }

@@ -80,8 +80,14 @@ cudaError_t launch_gemm_ln(const CUtensorMap &tmA, const WeightMaps &W, const CU
 void gemm_ln_set_trace(long long *dev_buf);
 
 // ---- rowwise.cu -----------------------------------------------------------------------------
-// cu_seqlens (exclusive prefix sum of lens, n_seq+1 entries) and per-token position inside its sentence
-cudaError_t launch_pack(const int32_t *lens, int n_seq, int32_t *cu_seqlens, int32_t *pos, int T, cudaStream_t st);
+// the on-device batcher: sentences in the caller's order (ids concatenated in tok_in, lens) -> sorted by length (longest first) and
+// packed: tok / pos [T], cu [n_seq+1], order[s] = caller index of sorted sentence s; src_off / caller_off: scratch [n_seq]
+struct BatcherParams {
+    const int32_t *tok_in, *lens;
+    int n_seq, T;
+    int32_t *tok, *pos, *cu, *order, *src_off, *caller_off;
+};
+cudaError_t launch_batcher(const BatcherParams &b, cudaStream_t st);
 // x = LN(word[tok] + type[0] + pos[p]) * gamma + beta ; tables in their GGUF storage type
 struct EmbedParams {
     const void *word, *type, *posw;  // tables, raw GGUF bytes on device
@@ -97,7 +103,8 @@ struct EmbedParams {
 cudaError_t launch_embed_ln(const EmbedParams &p, cudaStream_t st);
 cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *beta, int T, int d, float eps,
                           __half *y, __half *yq, int qmode, cudaStream_t st);
-cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, int n_seq, int d, float *out, cudaStream_t st);
+// sentence s (rows cu[s]..cu[s+1] of x) -> out row order[s] (order == nullptr: row s)
+cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, const int32_t *order, int n_seq, int d, float *out, cudaStream_t st);
 
 // ---- attention_tc.cu ------------------------------------------------------------------------
 // qkv [T][3d] f16 (Q | K | V along the row) read through tmQKV (make_tmap_attention), out [T][d] f16;

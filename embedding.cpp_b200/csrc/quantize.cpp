@@ -104,7 +104,7 @@ extern "C" BERT_API bool bert_model_quantize(const char *fname_inp, const char *
     GgufFile g;
     std::string err;
     if (!g.open(fname_inp, err)) { fprintf(stderr, "%s: failed to open '%s': %s\n", __func__, fname_inp, err.c_str()); return false; }
-    const uint32_t AL = 32;
+    const uint32_t AL = g.alignment;  // the input's general.alignment KV is carried over verbatim, so the output must honour it (default 32)
     std::vector<uint8_t> head;
     head.insert(head.end(), {'G', 'G', 'U', 'F'});
     put<uint32_t>(head, 3);

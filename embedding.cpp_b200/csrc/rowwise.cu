@@ -1,6 +1,6 @@
 // rowwise.cu -- the HBM-bound kernels of the encoder, one warp per token row, warp-shuffle
 // reductions, 16-byte vector accesses:
-//   pack_kernel       on-device batcher tail: cu_seqlens (prefix sum of lengths) + per-token position
+//   batch_sort/pack   the on-device batcher: sentences sorted by length, packed; cu_seqlens, positions, output order
 //   embed_ln_kernel   gather(word,type,pos) + add + LayerNorm            (bert.cpp:868-898)
 //   add_ln_kernel     LayerNorm of the pre-LN sum the GEMM epilogue wrote (bert.cpp:958-963, 981-992)
 //   pool_norm_kernel  mean over the sentence's tokens + L2 normalise      (bert.cpp:995-1006)
@@ -17,46 +17,123 @@ namespace bk {
 
 constexpr int kMaxChunks = 8;  // 8 halves per chunk, 32 lanes -> d <= 2048
 
-// ------------------------------------------------------------------------------------- pack
-// lens[n_seq] -> cu[n_seq+1]; pos[t] = t - cu[seq(t)].  Single CTA scan (n_seq is at most a few
-// thousand per launch), then all CTAs fill positions by binary search over cu.
-__global__ void pack_scan_kernel(const int32_t *__restrict__ lens, int n_seq, int32_t *__restrict__ cu) {
-    pdl_launch_dependents();
-    pdl_wait();
-    __shared__ int32_t warp_tot[32];
-    __shared__ int32_t carry_s;
-    if (threadIdx.x == 0) { carry_s = 0; cu[0] = 0; }
+// ------------------------------------------------------------------------------------- batcher
+// The on-device batcher.  Input: the sentences of one micro-batch in the CALLER'S order -- ids concatenated (tok_in) and
+// lens[n_seq].  batch_sort_kernel (one CTA): stable counting sort of the sentences by length, longest first (keys 1..512:
+// histogram -> descending bin starts -> ranks), then for the sorted order s: order[s] = caller index, cu[s+1] = packed token
+// offset (prefix sum of the sorted lengths), src_off[s] = where that sentence starts in tok_in.  batch_pack_kernel (all
+// CTAs): packed token t -> its sentence s (binary search over cu), pos[t] = t - cu[s], tok[t] = tok_in[src_off[s] + pos].
+// Everything downstream works on the packed, length-sorted layout (the attention kernels take the sentences of more than 128
+// tokens as a prefix); pool_norm writes sentence s to output row order[s], so results leave in the caller's order.
+// The reference has no batcher: bert_eval_batch loops over the sentences one graph at a time (bert.cpp:1065).
+constexpr int kMaxLen = 512;
+
+// inclusive block scan of one value per thread (1024 threads); returns the inclusive prefix, *total = sum over the block
+__device__ __forceinline__ int block_scan_incl(int v, int32_t *warp_tot, int *total) {
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane_id() >= o) incl += n;
+    }
+    __syncthreads();  // warp_tot reuse
+    if (lane_id() == 31) warp_tot[threadIdx.x >> 5] = incl;
     __syncthreads();
-    for (int base = 0; base < n_seq; base += blockDim.x) {
-        const int i = base + threadIdx.x;
-        int v = (i < n_seq) ? lens[i] : 0;
-        int incl = v;
+    if (threadIdx.x < 32) {
+        const int w = (threadIdx.x < (blockDim.x >> 5)) ? warp_tot[threadIdx.x] : 0;
+        int wi = w;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            int n = __shfl_up_sync(0xffffffffu, incl, o);
-            if ((int)lane_id() >= o) incl += n;
+            const int n = __shfl_up_sync(0xffffffffu, wi, o);
+            if ((int)lane_id() >= o) wi += n;
         }
-        if (lane_id() == 31) warp_tot[threadIdx.x >> 5] = incl;
+        warp_tot[threadIdx.x] = wi - w;  // exclusive warp offsets
+        if (threadIdx.x == 31) warp_tot[32] = wi;
+    }
+    __syncthreads();
+    *total = warp_tot[32];
+    return incl + warp_tot[threadIdx.x >> 5];
+}
+
+__global__ void __launch_bounds__(1024) batch_sort_kernel(const int32_t *__restrict__ lens, int n_seq, int32_t *__restrict__ order,
+                                                          int32_t *__restrict__ cu, int32_t *__restrict__ src_off,
+                                                          int32_t *__restrict__ caller_off) {
+    pdl_launch_dependents();
+    pdl_wait();
+    __shared__ int32_t cursor[kMaxLen + 2];  // histogram, then running output position per length
+    __shared__ int32_t warp_tot[33];
+    const int tid = threadIdx.x;
+    if (n_seq == 1) {  // latency path: nothing to sort
+        if (tid == 0) { order[0] = 0; src_off[0] = 0; cu[0] = 0; cu[1] = min(max(lens[0], 1), kMaxLen); }
+        return;
+    }
+    for (int k = tid; k < kMaxLen + 2; k += blockDim.x) cursor[k] = 0;
+    __syncthreads();
+    // histogram of lengths + caller-order token offsets (exclusive scan of lens in the caller's order)
+    int carry = 0;
+    for (int base = 0; base < n_seq; base += blockDim.x) {
+        const int i = base + tid;
+        const int v = (i < n_seq) ? min(max(lens[i], 1), kMaxLen) : 0;
+        if (i < n_seq) atomicAdd(&cursor[v], 1);
+        int tot;
+        const int incl = block_scan_incl(v, warp_tot, &tot);
+        if (i < n_seq) caller_off[i] = carry + incl - v;
+        carry += tot;
+    }
+    __syncthreads();
+    // descending bin starts: start[len] = number of sentences longer than len  (bins kMaxLen .. 1 scanned in that order)
+    {
+        const int len = kMaxLen - tid;  // thread 0 <-> longest
+        const int v = (len >= 1) ? cursor[len] : 0;
+        int tot;
+        const int incl = block_scan_incl(v, warp_tot, &tot);
         __syncthreads();
-        if (threadIdx.x < 32) {
-            int w = (threadIdx.x < (blockDim.x >> 5)) ? warp_tot[threadIdx.x] : 0;
-            int wi = w;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                int n = __shfl_up_sync(0xffffffffu, wi, o);
-                if ((int)lane_id() >= o) wi += n;
+        if (len >= 1) cursor[len] = incl - v;
+    }
+    __syncthreads();
+    // stable ranks: chunks of 1024 sentences, the warps of a chunk take their turn in order; inside a warp the lanes with the same
+    // length are ranked by lane (match_any), the lowest of them advances the bin's cursor
+    for (int base = 0; base < n_seq; base += blockDim.x) {
+        const int i = base + tid;
+        const bool ok = i < n_seq;
+        const int key = ok ? min(max(lens[i], 1), kMaxLen) : 0;  // key 0: idle lanes group among themselves
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        const int rank = __popc(peers & ((1u << lane_id()) - 1u));
+        const int cnt = __popc(peers);
+        const int n_warps = (min(n_seq - base, (int)blockDim.x) + 31) >> 5;
+        for (int w = 0; w < n_warps; w++) {
+            if ((tid >> 5) == w && ok) {
+                const int dst = cursor[key] + rank;
+                order[dst] = i;
+                __syncwarp(peers);
+                if (rank == 0) cursor[key] += cnt;
             }
-            warp_tot[threadIdx.x] = wi - w;  // exclusive warp offsets
+            __syncthreads();
         }
-        __syncthreads();
-        const int tot = incl + warp_tot[threadIdx.x >> 5] + carry_s;
-        if (i < n_seq) cu[i + 1] = tot;
-        __syncthreads();
-        if (threadIdx.x == blockDim.x - 1) carry_s = tot;
-        __syncthreads();
+    }
+    __threadfence_block();
+    __syncthreads();
+    // packed offsets in sorted order
+    if (tid == 0) cu[0] = 0;
+    carry = 0;
+    for (int base = 0; base < n_seq; base += blockDim.x) {
+        const int s = base + tid;
+        int v = 0, src = 0;
+        if (s < n_seq) {
+            src = order[s];
+            v = min(max(lens[src], 1), kMaxLen);
+        }
+        int tot;
+        const int incl = block_scan_incl(v, warp_tot, &tot);
+        if (s < n_seq) {
+            cu[s + 1] = carry + incl;
+            src_off[s] = caller_off[src];
+        }
+        carry += tot;
     }
 }
-__global__ void pack_pos_kernel(const int32_t *__restrict__ cu, int n_seq, int32_t *__restrict__ pos, int T) {
+__global__ void batch_pack_kernel(const int32_t *__restrict__ tok_in, const int32_t *__restrict__ cu, const int32_t *__restrict__ src_off,
+                                  int n_seq, int32_t *__restrict__ tok, int32_t *__restrict__ pos, int T) {
     pdl_launch_dependents();
     pdl_wait();
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -66,17 +143,20 @@ __global__ void pack_pos_kernel(const int32_t *__restrict__ cu, int n_seq, int32
         const int mid = (lo + hi) >> 1;
         if (__ldg(cu + mid) <= t) lo = mid; else hi = mid;
     }
-    pos[t] = t - __ldg(cu + lo);
+    const int p = t - __ldg(cu + lo);
+    pos[t] = p;
+    tok[t] = __ldg(tok_in + __ldg(src_off + lo) + p);
 }
-cudaError_t launch_pack(const int32_t *lens, int n_seq, int32_t *cu_seqlens, int32_t *pos, int T, cudaStream_t st) {
+cudaError_t launch_batcher(const BatcherParams &b, cudaStream_t st) {
     {
         LaunchConfig lc(dim3(1), dim3(1024), 0, st);
-        cudaError_t err = cudaLaunchKernelEx(&lc.cfg, pack_scan_kernel, lens, n_seq, cu_seqlens);
+        cudaError_t err = cudaLaunchKernelEx(&lc.cfg, batch_sort_kernel, b.lens, b.n_seq, b.order, b.cu, b.src_off, b.caller_off);
         if (err != cudaSuccess) return err;
     }
     {
-        LaunchConfig lc(dim3((unsigned)((T + 255) / 256)), dim3(256), 0, st);
-        cudaError_t err = cudaLaunchKernelEx(&lc.cfg, pack_pos_kernel, (const int32_t *)cu_seqlens, n_seq, pos, T);
+        LaunchConfig lc(dim3((unsigned)((b.T + 255) / 256)), dim3(256), 0, st);
+        cudaError_t err = cudaLaunchKernelEx(&lc.cfg, batch_pack_kernel, b.tok_in, (const int32_t *)b.cu, (const int32_t *)b.src_off, b.n_seq, b.tok,
+                                             b.pos, b.T);
         if (err != cudaSuccess) return err;
     }
     return cudaGetLastError();
@@ -279,7 +359,7 @@ cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *be
 // One CTA per sentence.  e[k] = sum_t x[t][k] * (1/L) (the reference multiplies by a vector of 1/L,
 // bert.cpp:999-1001), out = e * (1/sqrt(sum e^2)) (bert.cpp:1004-1006).
 __global__ void __launch_bounds__(256) pool_norm_kernel(const __half *__restrict__ x, const int32_t *__restrict__ cu,
-                                                        int d, float *__restrict__ out) {
+                                                        const int32_t *__restrict__ order, int d, float *__restrict__ out) {
     pdl_launch_dependents();
     pdl_wait();
     extern __shared__ float sacc[];  // [ngroups][d]
@@ -324,16 +404,17 @@ __global__ void __launch_bounds__(256) pool_norm_kernel(const __half *__restrict
 #pragma unroll
     for (int w = 0; w < 8; w++) tot += red[w];
     const float inv = 1.0f / sqrtf(tot);
-    for (int k = threadIdx.x; k < d; k += blockDim.x) out[(size_t)s * d + k] = sacc[k] * inv;
+    const int row = order ? __ldg(order + s) : s;  // the batcher's sorted position -> the caller's sentence index
+    for (int k = threadIdx.x; k < d; k += blockDim.x) out[(size_t)row * d + k] = sacc[k] * inv;
 }
-cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, int n_seq, int d, float *out, cudaStream_t st) {
+cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, const int32_t *order, int n_seq, int d, float *out, cudaStream_t st) {
     if (d % 8 != 0) return cudaErrorInvalidValue;
     const int nch = d >> 3;
     const int cpr = nch < 256 ? nch : 256;
     const int groups = 256 / cpr > 0 ? 256 / cpr : 1;
     const size_t smem = (size_t)groups * d * sizeof(float);
     LaunchConfig lc(dim3((unsigned)n_seq), dim3(256), smem, st);
-    cudaLaunchKernelEx(&lc.cfg, pool_norm_kernel, x, cu_seqlens, d, out);
+    cudaLaunchKernelEx(&lc.cfg, pool_norm_kernel, x, cu_seqlens, order, d, out);
     return cudaGetLastError();
 }
 

@@ -32,7 +32,10 @@ int upload_lens(const int32_t *lens, int n_seq, DevBuf &d_lens, DevBuf &d_cu, De
     TCK(d_cu.alloc(((size_t)n_seq + 1) * 4));
     TCK(d_pos.alloc((size_t)T * 4));
     TCK(cudaMemcpy(d_lens.p, lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice));
-    TCK(launch_pack(d_lens.as<int32_t>(), n_seq, d_cu.as<int32_t>(), d_pos.as<int32_t>(), T, st));
+    std::vector<int32_t> cu(n_seq + 1, 0);  // the kernels under test take the sentences in the given order
+    for (int i = 0; i < n_seq; i++) cu[i + 1] = cu[i] + lens[i];
+    TCK(cudaMemcpy(d_cu.p, cu.data(), ((size_t)n_seq + 1) * 4, cudaMemcpyHostToDevice));
+    (void)st;
     *T_out = T; *max_out = mx;
     return 0;
 }
@@ -205,9 +208,59 @@ BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t 
     if (upload_lens(lens, n_seq, dL, dC, dPos, &T, &mx, 0)) return -1;
     TCK(dX.alloc((size_t)T * d * 2)); TCK(dO.alloc((size_t)n_seq * d * 4));
     TCK(cudaMemcpy(dX.p, x, (size_t)T * d * 2, cudaMemcpyHostToDevice));
-    TCK(launch_pool_norm(dX.as<__half>(), dC.as<int32_t>(), n_seq, d, dO.as<float>(), 0));
+    TCK(launch_pool_norm(dX.as<__half>(), dC.as<int32_t>(), nullptr, n_seq, d, dO.as<float>(), 0));
     TCK(cudaDeviceSynchronize());
     TCK(cudaMemcpy(out, dO.p, (size_t)n_seq * d * 4, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+BK_API int bk_test_batcher(int device, int32_t n_seq, const int32_t *lens, const int32_t *tokens, int32_t *order, int32_t *cu,
+                           int32_t *tok, int32_t *pos) {
+    TCK(cudaSetDevice(device));
+    int T = 0;
+    for (int i = 0; i < n_seq; i++) T += lens[i];
+    DevBuf dL, dTin, dTok, dPos, dCu, dOrd, dSrc, dOff;
+    TCK(dL.alloc((size_t)n_seq * 4)); TCK(dTin.alloc((size_t)T * 4)); TCK(dTok.alloc((size_t)T * 4)); TCK(dPos.alloc((size_t)T * 4));
+    TCK(dCu.alloc(((size_t)n_seq + 1) * 4)); TCK(dOrd.alloc((size_t)n_seq * 4)); TCK(dSrc.alloc((size_t)n_seq * 4)); TCK(dOff.alloc((size_t)n_seq * 4));
+    TCK(cudaMemcpy(dL.p, lens, (size_t)n_seq * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dTin.p, tokens, (size_t)T * 4, cudaMemcpyHostToDevice));
+    BatcherParams b{dTin.as<int32_t>(), dL.as<int32_t>(), n_seq, T, dTok.as<int32_t>(), dPos.as<int32_t>(), dCu.as<int32_t>(),
+                    dOrd.as<int32_t>(), dSrc.as<int32_t>(), dOff.as<int32_t>()};
+    TCK(launch_batcher(b, 0));
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(order, dOrd.p, (size_t)n_seq * 4, cudaMemcpyDeviceToHost));
+    TCK(cudaMemcpy(cu, dCu.p, ((size_t)n_seq + 1) * 4, cudaMemcpyDeviceToHost));
+    TCK(cudaMemcpy(tok, dTok.p, (size_t)T * 4, cudaMemcpyDeviceToHost));
+    TCK(cudaMemcpy(pos, dPos.p, (size_t)T * 4, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+BK_API int bk_test_embed_ln(int device, int32_t T, int32_t d, int32_t n_vocab, int32_t n_pos, int32_t wtype, const void *word, const void *type,
+                            const void *posw, const float *gamma, const float *beta, float eps, const int32_t *tokens, const int32_t *pos,
+                            int32_t qmode, uint16_t *x, uint16_t *xq) {
+    TCK(cudaSetDevice(device));
+    auto row_bytes = [&](int64_t rows) -> size_t {
+        return wtype == BK_F32 ? (size_t)rows * d * 4 : wtype == BK_F16 ? (size_t)rows * d * 2 : (size_t)rows * (d / 32) * (wtype == BK_Q4_0 ? 18 : 20);
+    };
+    DevBuf dW, dT, dP, dG, dB, dTok, dPos, dX, dXq;
+    TCK(dW.alloc(row_bytes(n_vocab))); TCK(dT.alloc(row_bytes(2))); TCK(dP.alloc(row_bytes(n_pos)));
+    TCK(dG.alloc((size_t)d * 4)); TCK(dB.alloc((size_t)d * 4)); TCK(dTok.alloc((size_t)T * 4)); TCK(dPos.alloc((size_t)T * 4));
+    TCK(dX.alloc((size_t)T * d * 2)); TCK(dXq.alloc((size_t)T * d * 2));
+    TCK(cudaMemcpy(dW.p, word, row_bytes(n_vocab), cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dT.p, type, row_bytes(2), cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dP.p, posw, row_bytes(n_pos), cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dG.p, gamma, (size_t)d * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dB.p, beta, (size_t)d * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dTok.p, tokens, (size_t)T * 4, cudaMemcpyHostToDevice));
+    TCK(cudaMemcpy(dPos.p, pos, (size_t)T * 4, cudaMemcpyHostToDevice));
+    EmbedParams p;
+    p.word = dW.p; p.type = dT.p; p.posw = dP.p; p.wtype = wtype; p.gamma = dG.as<float>(); p.beta = dB.as<float>();
+    p.tokens = dTok.as<int32_t>(); p.pos = dPos.as<int32_t>(); p.T = T; p.d = d; p.n_vocab = n_vocab; p.eps = eps;
+    p.x = dX.as<__half>(); p.xq = dXq.as<__half>(); p.qmode = qmode;
+    TCK(launch_embed_ln(p, 0));
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(x, dX.p, (size_t)T * d * 2, cudaMemcpyDeviceToHost));
+    if (qmode && xq) TCK(cudaMemcpy(xq, dXq.p, (size_t)T * d * 2, cudaMemcpyDeviceToHost));
     return 0;
 }
 

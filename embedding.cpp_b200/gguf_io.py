@@ -277,18 +277,32 @@ def write_bert_gguf(path: str, hp: BertHParams, weights: dict[str, np.ndarray], 
     if wt in (GGML_Q4_0, GGML_Q4_1):
         kvs += [_kv("general.quantization_version", T_U32, 2), _kv("general.file_type", T_U32, wt)]
 
-    infos, blobs, off = [], [], 0
+    tensors = []
     for name, shape in tensor_names(hp):
         w = np.ascontiguousarray(weights[name], dtype=np.float32)
         assert w.shape == shape, (name, w.shape, shape)
         t = wt if (w.ndim == 2 and name.endswith("weight")) else GGML_F32
-        if t == GGML_F32:
-            raw = w.tobytes()
-        elif t == GGML_F16:
-            raw = w.astype(np.float16).tobytes()
-        else:
-            w16 = w.astype(np.float16).astype(np.float32)
-            raw = (quantize_q4_0 if t == GGML_Q4_0 else quantize_q4_1)(w16).tobytes()
+        tensors.append((name, shape, t, encode_tensor(w, t)))
+    write_gguf(path, kvs, tensors)
+
+
+def encode_tensor(w: np.ndarray, t: int) -> bytes:
+    """f32 array -> raw bytes of ggml type `t`.  Q4 blocks are taken from the f16-rounded values, i.e. what the
+    reference's quantize tool sees when it is fed the F16 file (models/run_conversions.sh:7-8)."""
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    if t == GGML_F32:
+        return w.tobytes()
+    if t == GGML_F16:
+        return w.astype(np.float16).tobytes()
+    w16 = w.astype(np.float16).astype(np.float32)
+    return (quantize_q4_0 if t == GGML_Q4_0 else quantize_q4_1)(w16).tobytes()
+
+
+def write_gguf(path: str, kvs: list[bytes], tensors: list[tuple]) -> None:
+    """Container writer (ggml.c:18017-18306 reads it back): header, KV section (`kvs` = records made by _kv), tensor
+    infos, padding to ALIGNMENT, tensor data each padded to ALIGNMENT.  `tensors` = (name, numpy shape, ggml type, raw bytes)."""
+    infos, blobs, off = [], [], 0
+    for name, shape, t, raw in tensors:
         ne = tuple(reversed(shape))
         infos.append(_s(name) + struct.pack("<I", len(ne)) + struct.pack(f"<{len(ne)}Q", *ne)
                      + struct.pack("<IQ", t, off))

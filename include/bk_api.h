@@ -12,6 +12,7 @@
 #ifndef BK_API_H
 #define BK_API_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #define BK_API __attribute__((visibility("default")))
@@ -67,6 +68,22 @@ BK_API int bk_engine_forward(bk_engine *e, const int32_t *tokens, const int32_t 
  * slot s, the batch submitted to slot 1-s is already running. */
 BK_API int bk_engine_submit(bk_engine *e, int32_t slot, const int32_t *tokens, const int32_t *lens, int32_t n_seq);
 BK_API int bk_engine_collect(bk_engine *e, int32_t slot, float *out);
+/* submit straight from the caller's ragged arrays (bert_eval_batch's `batch_tokens` / `n_tokens`, bert.h:79-85): sent_tokens[i] points at
+ * sentence i's ids, sent_lens[i] is its length, in the CALLER'S order -- sorting by length, packing and positions happen on the device
+ * (rowwise.cu: batch_sort / batch_pack; the reference loops over sentences instead, bert.cpp:1065).  The n_seq embeddings are copied,
+ * in the caller's order, to host_out (pinned memory from bk_host_alloc; NULL = the slot's own buffer, fetched by bk_engine_collect(out)).
+ * bk_engine_collect(e, slot, NULL) then only waits for the batch. */
+BK_API int bk_engine_submit_ragged(bk_engine *e, int32_t slot, const int32_t *const *sent_tokens, const int32_t *sent_lens, int32_t n_seq,
+                                   float *host_out);
+/* page-locked host memory usable by every engine's stream as an asynchronous copy target */
+BK_API void *bk_host_alloc(size_t bytes);
+BK_API void  bk_host_free(void *p);
+/* the small-batch (latency) path replays captured CUDA graphs: launches served by a replay, shapes captured (on their second
+ * sighting), launches done directly (first sighting) since the engine was created */
+BK_API int bk_engine_graph_stats(bk_engine *e, int64_t *replayed, int64_t *captured, int64_t *direct);
+/* the same counters summed over the engines of a bert.h context (`ctx` = what bert_load_from_file returned) */
+struct bert_ctx;
+BK_API int bk_bert_graph_stats(struct bert_ctx *ctx, int64_t *replayed, int64_t *captured, int64_t *direct);
 
 /* Same work with the inputs already resident in HBM (bench.py `value` leg): stage a whole job once
  * (any number of sentences, in the caller's order; it is cut into micro-batches of <= cap_tokens /
@@ -113,6 +130,16 @@ BK_API int bk_test_attention(int device, int32_t n_seq, const int32_t *lens, int
                              const uint16_t *qkv, int32_t qmode, uint16_t *out);
 /* mean over tokens + L2 normalise; bert.cpp:995-1006 */
 BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t d, const uint16_t *x, float *out);
+/* the on-device batcher alone: lens[n_seq] and the ids concatenated in the caller's order -> order[n_seq] (sorted position ->
+ * caller index; stable, longest first), cu[n_seq+1], packed tok[T] and pos[T] */
+BK_API int bk_test_batcher(int device, int32_t n_seq, const int32_t *lens, const int32_t *tokens, int32_t *order, int32_t *cu,
+                           int32_t *tok, int32_t *pos);
+/* embeddings gather + LayerNorm alone: x = LN((type[0] + word[tok]) + pos[p]) * gamma + beta, tables as raw GGUF bytes of `wtype`
+ * (word [n_vocab][d], type [2][d], posw [n_pos][d]); x f16 [T][d], xq its Q8-rounded copy (qmode 1 / 2).  bert.cpp:868-898,
+ * ggml_get_rows ggml.c:10108-10224 */
+BK_API int bk_test_embed_ln(int device, int32_t T, int32_t d, int32_t n_vocab, int32_t n_pos, int32_t wtype, const void *word, const void *type,
+                            const void *posw, const float *gamma, const float *beta, float eps, const int32_t *tokens, const int32_t *pos,
+                            int32_t qmode, uint16_t *x, uint16_t *xq);
 
 /* ---- host-side tokenizer alone (no GPU needed; tests/test_tokenizer.py) -------------------------
  * Replaces bert_tokenizer::load / encode (tokenizer.cpp:30-53 -> Rust tokenizers crate):

@@ -15,8 +15,15 @@
 #       P2a bert.cpp:826   1 GiB compute-arena cap -> 64 GiB
 #       P2b bert.cpp:814   arena head-room 1.1 -> 4.0 (O(N^2) attention
 #           tensors are not in the 4-token dry run; N>=384 aborts otherwise)
+#
+#   VARIANT=portable ./build_ref.sh  builds oracle/_ref/libbert_ref_portable.so instead: the same sources
+#   WITHOUT -mavx -mavx2 -mfma -mf16c, i.e. the reference's own generic-C code paths (the `#else` branches
+#   of ggml-quants.c:632-700,2426-2523 / ggml.c that it runs on a CPU without AVX2).  Used only to
+#   measure how far two builds of the REFERENCE ITSELF are apart (tests/golden: emb_portable): the Q8
+#   activation rounding makes deep Q4 models chaotic, so that spread is the floor of any re-implementation.
 set -euo pipefail
 REF=${REF:-/root/reference}
+VARIANT=${VARIANT:-avx2}
 HERE=$(cd "$(dirname "$0")" && pwd)
 OUT=$HERE/_ref
 if [ ! -f "$REF/bert.cpp" ]; then
@@ -25,7 +32,9 @@ fi
 mkdir -p "$OUT"
 TMP=$(mktemp -d)
 trap 'rm -rf "$TMP"' EXIT
-CF="-O3 -mavx -mavx2 -mfma -mf16c -D_GNU_SOURCE -D_XOPEN_SOURCE=600 -fPIC -DNDEBUG \
+SIMD="-mavx -mavx2 -mfma -mf16c"; LIBNAME=libbert_ref.so
+if [ "$VARIANT" = "portable" ]; then SIMD=""; LIBNAME=libbert_ref_portable.so; fi
+CF="-O3 $SIMD -D_GNU_SOURCE -D_XOPEN_SOURCE=600 -fPIC -DNDEBUG \
     -I$REF/ggml/include -I$REF/ggml/include/ggml -I$REF/ggml/src"
 pids=()
 for f in ggml ggml-alloc ggml-backend ggml-quants; do
@@ -41,5 +50,5 @@ g++ -std=c++17 $CF -w -include unordered_map -include mutex -include array -incl
     -I"$REF" -I"$HERE/ref_shim" -c "$TMP/bert_patched.cpp" -o "$TMP/bert.o" & pids+=($!)
 g++ -std=c++17 $CF -w -I"$REF" -I"$HERE/ref_shim" -c "$HERE/ref_shim/tok_shim.cpp" -o "$TMP/tok_shim.o" & pids+=($!)
 for p in "${pids[@]}"; do wait "$p"; done
-g++ -shared -o "$OUT/libbert_ref.so" "$TMP"/*.o -lpthread -lm
-echo "build_ref: wrote $OUT/libbert_ref.so"
+g++ -shared -o "$OUT/$LIBNAME" "$TMP"/*.o -lpthread -lm
+echo "build_ref: wrote $OUT/$LIBNAME"

@@ -18,5 +18,13 @@ def load_golden(name):
     for L in lens:
         toks.append(z["tokens"][off:off + L].astype(np.int32))
         off += L
+    emb = z["emb"]
+    # emb_portable: the same sentences through the reference's portable (non-AVX2) build; spread = 1 - cos between the two
+    # builds of the reference itself = the reproducibility floor of that model and sentence (tests/golden/gen_golden.py)
+    port = z["emb_portable"] if "emb_portable" in z.files else None
+    spread = None
+    if port is not None:
+        a, b = emb.astype(np.float64), port.astype(np.float64)
+        spread = 1.0 - (a * b).sum(1) / (np.linalg.norm(a, axis=1) * np.linalg.norm(b, axis=1))
     return dict(shape=str(z["shape"]), ftype=str(z["ftype"]), seed=int(z["seed"]), n_vocab=int(z["n_vocab"]),
-                dist=str(z["dist"]), tokens=toks, emb=z["emb"])
+                dist=str(z["dist"]), tokens=toks, emb=emb, emb_portable=port, spread=spread)

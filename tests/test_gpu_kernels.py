@@ -176,8 +176,10 @@ def test_add_ln(lib, orc, make_model, T, d, qmode):
         err = np.abs(yq.astype(np.float32) - want)
         step = np.abs(ref).reshape(T, d // 32, 32).max(-1, keepdims=True) / 127.0
         step = np.broadcast_to(step, (T, d // 32, 32)).reshape(T, d)
-        # fp32-vs-double LN sums can flip a rounding decision for values sitting on a .5 boundary
-        assert (err <= 1e-3 * np.abs(want) + 1e-6).mean() > 0.995
+        # fp32-vs-double LN sums can flip a rounding decision for values sitting on a .5 boundary: count them, never more than one step
+        flips = int((err > 1e-3 * np.abs(want) + 1e-6).sum())
+        print(f"\nadd_ln T={T} d={d} qmode={qmode}: {flips} of {err.size} Q8 roundings flipped by one step ({flips / err.size:.2e})")
+        assert flips <= 0.005 * err.size
         assert (err <= step * 1.01 + 1e-3).all()
 
 
@@ -215,7 +217,10 @@ def test_gemm_ln_fused(lib, orc, make_model, M, N, K, qmode):
         step = np.abs(ref).reshape(M, N // 32, 32).max(-1, keepdims=True) / 127.0
         step = np.broadcast_to(step, (M, N // 32, 32)).reshape(M, N)
         errq = np.abs(yq.astype(np.float32) - want)
-        assert (errq <= 1e-3 * np.abs(want) + 1e-5).mean() > 0.99   # fp32 GEMM-order differences can flip a .5 rounding
+        # fp32 GEMM-order differences can flip a .5 rounding: count them, never more than one step
+        flips = int((errq > 1e-3 * np.abs(want) + 1e-5).sum())
+        print(f"\ngemm_ln M={M} N={N} K={K} qmode={qmode}: {flips} of {errq.size} Q8 roundings flipped by one step ({flips / errq.size:.2e})")
+        assert flips <= 0.01 * errq.size
         assert (errq <= step * 1.01 + 2e-3).all()
 
 
@@ -310,3 +315,66 @@ def test_pool_norm(lib, orc, make_model, d, lens):
         ref = o.pool(x[off:off + n].astype(np.float32))
         assert np.allclose(out[i], ref, rtol=1e-5, atol=1e-6)
         off += n
+
+
+@pytest.mark.parametrize("n_seq", [1, 2, 31, 32, 33, 1000, 1024, 1025, 5000, 8192])
+def test_on_device_batcher(lib, n_seq):
+    """batch_sort + batch_pack (rowwise.cu): stable sort by length, longest first; packed ids, positions, cu_seqlens and the
+    sorted-position -> caller-index map must equal NumPy's stable argsort.  Integer work: bit-exact."""
+    rng = np.random.default_rng(n_seq)
+    lens = rng.integers(1, 513, n_seq).astype(np.int32)
+    if n_seq >= 1000:
+        lens[rng.integers(0, n_seq, n_seq // 3)] = 128          # many ties: stability matters
+    toks = rng.integers(0, 30522, int(lens.sum())).astype(np.int32)
+    T = int(lens.sum())
+    order, cu = np.zeros(n_seq, np.int32), np.zeros(n_seq + 1, np.int32)
+    tok, pos = np.zeros(T, np.int32), np.zeros(T, np.int32)
+    p = lambda a: a.ctypes.data_as(_i32p)
+    assert lib.bk_test_batcher(0, n_seq, p(lens), p(toks), p(order), p(cu), p(tok), p(pos)) == 0
+    want_order = np.argsort(-lens.astype(np.int64), kind="stable").astype(np.int32)
+    assert np.array_equal(order, want_order)
+    want_cu = np.concatenate([[0], np.cumsum(lens[want_order])]).astype(np.int32)
+    assert np.array_equal(cu, want_cu)
+    src = np.concatenate([[0], np.cumsum(lens)])[:-1]
+    want_tok = np.concatenate([toks[src[i]:src[i] + lens[i]] for i in want_order])
+    want_pos = np.concatenate([np.arange(lens[i]) for i in want_order]).astype(np.int32)
+    assert np.array_equal(tok, want_tok) and np.array_equal(pos, want_pos)
+
+
+@pytest.mark.parametrize("ftype", ["f32", "f16", "q4_0", "q4_1"])
+@pytest.mark.parametrize("shape", ["mini", "mini384", "bert-base"])
+def test_embed_ln(lib, binding, gio, orc, make_model, shape, ftype):
+    """embeddings gather (three tables in their GGUF storage type, decoded in registers) + LayerNorm alone against the oracle's
+    embed (bert.cpp:868-898: (type[0] + word[tok]) + pos[i], ggml_get_rows decode, LayerNorm with double sums); for Q4
+    files also the Q8-rounded copy against the oracle's round trip of ITS OWN LayerNorm output (flipped roundings counted)."""
+    path = make_model(shape, ftype, seed=51, n_vocab=600)
+    f = gio.read_gguf(path)
+    hp = f.hparams()
+    o = orc.Oracle(path)
+    rng = np.random.default_rng(7)
+    tokens = rng.integers(0, hp.n_vocab, 300).astype(np.int32)
+    want = o.embed(tokens)                                    # positions 0..T-1
+    pos = np.arange(len(tokens), dtype=np.int32)
+    d, T = hp.n_embd, len(tokens)
+    t = {k: np.ascontiguousarray(f.tensors[k][2]) for k in ("embeddings.word_embeddings.weight", "embeddings.token_type_embeddings.weight",
+                                                              "embeddings.position_embeddings.weight")}
+    gamma, beta = f.f32("embeddings.LayerNorm.weight"), f.f32("embeddings.LayerNorm.bias")
+    qmode = {"q4_0": 1, "q4_1": 2}.get(ftype, 0)
+    x, xq = np.zeros((T, d), np.float16), np.zeros((T, d), np.float16)
+    wtype = f.tensors["embeddings.word_embeddings.weight"][0]
+    assert lib.bk_test_embed_ln(0, T, d, hp.n_vocab, hp.n_max_tokens, wtype, t["embeddings.word_embeddings.weight"].ctypes.data,
+                                t["embeddings.token_type_embeddings.weight"].ctypes.data, t["embeddings.position_embeddings.weight"].ctypes.data,
+                                gamma.ctypes.data_as(_f32p), beta.ctypes.data_as(_f32p), hp.eps, tokens.ctypes.data_as(_i32p),
+                                pos.ctypes.data_as(_i32p), qmode, u16(x), u16(xq)) == 0
+    # x is the f16 rounding of the fp32 LayerNorm output: half an f16 ulp + fp32-vs-double statistics
+    err = np.abs(x.astype(np.float32) - want)
+    assert (err <= 6e-4 * np.abs(want) + 1e-6).all(), float((err / (np.abs(want) + 1e-6)).max())
+    if qmode:
+        rt = np.zeros_like(want)
+        fn = o.lib.oracle_quant_q8_0_roundtrip if qmode == 1 else o.lib.oracle_quant_q8_1_roundtrip
+        fn(np.ascontiguousarray(want).ctypes.data_as(_f32p), rt.ctypes.data_as(_f32p), want.size)
+        errq = np.abs(xq.astype(np.float32) - rt)
+        step = np.broadcast_to(np.abs(want).reshape(T, d // 32, 32).max(-1, keepdims=True) / 127.0, (T, d // 32, 32)).reshape(T, d)
+        flips = int((errq > 1e-3 * np.abs(rt) + 1e-6).sum())
+        print(f"\nembed_ln {shape} {ftype}: {flips} of {errq.size} Q8 roundings flipped by one step")
+        assert flips <= 0.002 * errq.size and (errq <= step * 1.01 + 1e-3).all()
