@@ -33,7 +33,16 @@ $(OBJ):
 oracle:
 	$(MAKE) -s -C oracle all
 
+# race / memory / barrier checking of every kernel of the path (the reference has BERT_SANITIZE_* host sanitizers, CMakeLists.txt:28-30,51-64;
+# here the hazards are on the device: hand-rolled mbarrier protocols, TMA / generic proxy hand-offs, TMEM aliasing).
+# One tool per GPU call:  gpurun -- make sanitize TOOL=memcheck   (then racecheck, synccheck); log -> gpurun_out/sanitize_$(TOOL).log
+TOOL ?= memcheck
+sanitize: all
+	mkdir -p gpurun_out
+	timeout 1500 compute-sanitizer --tool $(TOOL) --error-exitcode 9 --launch-timeout 120 python tools/sanitize_smoke.py > gpurun_out/sanitize_$(TOOL).log 2>&1; \
+	rc=$$?; tail -25 gpurun_out/sanitize_$(TOOL).log; echo "compute-sanitizer --tool $(TOOL): exit code $$rc"; exit $$rc
+
 clean:
 	rm -rf build
 
-.PHONY: all oracle clean
+.PHONY: all oracle clean sanitize

@@ -29,7 +29,7 @@ BERT_SYMBOLS = ["bert_load_from_file", "bert_free", "bert_encode", "bert_encode_
 BK_SYMBOLS = ["bk_device_count", "bk_last_error", "bk_engine_create", "bk_engine_destroy", "bk_engine_set_tensor",
               "bk_engine_finalize", "bk_engine_forward", "bk_engine_submit", "bk_engine_collect", "bk_engine_submit_ragged", "bk_host_alloc", "bk_host_free",
               "bk_engine_graph_stats", "bk_bert_graph_stats", "bk_engine_stage", "bk_engine_run_staged", "bk_engine_read_output",
-              "bk_engine_kernel_ms", "bk_engine_read_hidden", "bk_engine_set_keep_hidden", "bk_engine_launch_count", "bk_profiler_range",
+              "bk_engine_kernel_ms", "bk_engine_read_hidden", "bk_engine_set_keep_hidden", "bk_engine_launch_count", "bk_engine_check_guards", "bk_profiler_range",
               "bk_test_gemm", "bk_test_gemm_ln", "bk_test_gelu", "bk_test_add_ln", "bk_test_attention", "bk_test_pool", "bk_test_batcher", "bk_test_embed_ln",
               "bk_tokenizer_create", "bk_tokenizer_destroy", "bk_tokenizer_encode"]
 
@@ -104,6 +104,8 @@ def load_library(path: str | None = None):
     L.bk_engine_set_keep_hidden.argtypes = [vp, i32]
     L.bk_engine_launch_count.restype = i64
     L.bk_engine_launch_count.argtypes = [vp]
+    L.bk_engine_check_guards.restype = i64
+    L.bk_engine_check_guards.argtypes = [vp]
     L.bk_profiler_range.argtypes = [i32]
     L.bk_test_gemm.argtypes = [ctypes.c_int, i32, i32, i32, _u16p, vp, i32, _f32p, _u16p, i32, _u16p, _f32p]
     L.bk_test_gemm_ln.argtypes = [ctypes.c_int, i32, i32, i32, _u16p, _u16p, _f32p, _u16p, _f32p, _f32p, ctypes.c_float, i32, _u16p, _u16p, _f32p]
@@ -305,3 +307,9 @@ class Engine:
 
     def launch_count(self) -> int:
         return int(self.lib.bk_engine_launch_count(self.e))
+
+    def check_guards(self) -> int:
+        n = int(self.lib.bk_engine_check_guards(self.e))
+        if n < 0:
+            raise RuntimeError(self.lib.bk_last_error().decode())
+        return n

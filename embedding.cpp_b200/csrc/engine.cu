@@ -139,6 +139,11 @@ struct bk_engine {
     // the LayerNorm in the GEMM epilogue (gemm_ln.cu: a cluster per 256-row block); smaller ones have too few row blocks to
     // fill the clusters and use GEMM(+bias+residual) followed by add_ln.  BERT_B200_FUSED_LN_TOKENS; -1 = never
     int fused_ln_tokens = 4096;
+    // BERT_B200_GUARD=1 (tests; compute-sanitizer is closed on the GPU pool): every activation / index buffer is allocated with a
+    // 4 KB canary on both sides, bk_engine_check_guards() counts canary bytes a kernel has overwritten
+    struct Guarded { uint8_t *base; size_t bytes; };
+    std::vector<Guarded> guarded;
+    bool guard_on = false;
     // timing
     std::vector<cudaEvent_t> ev;
     std::vector<int> ev_kind;
@@ -147,6 +152,32 @@ struct bk_engine {
     int k_launches[BK_K_COUNT] = {0};
     int64_t launch_count = 0;
 };
+
+constexpr size_t kGuardBytes = 4096;
+constexpr int kGuardByte = 0xA5;
+// activation / index buffers go through here: plain cudaMalloc, or (guard mode) canaries on both sides
+template <class T>
+static cudaError_t act_alloc(bk_engine *e, T **p, size_t bytes) {
+    if (!e->guard_on) return cudaMalloc(p, bytes);
+    uint8_t *base = nullptr;
+    const size_t padded = (bytes + 255) & ~(size_t)255;
+    cudaError_t err = cudaMalloc(&base, padded + 2 * kGuardBytes);
+    if (err != cudaSuccess) return err;
+    err = cudaMemset(base, kGuardByte, padded + 2 * kGuardBytes);
+    if (err == cudaSuccess) err = cudaDeviceSynchronize();  // the engine's stream does not synchronise with the default stream
+    if (err != cudaSuccess) return err;
+    e->guarded.push_back({base, bytes});
+    *p = reinterpret_cast<T *>(base + kGuardBytes);
+    return cudaSuccess;
+}
+static void act_free(bk_engine *e, void *p) {
+    if (!p) return;
+    if (e->guard_on) {
+        for (auto &g : e->guarded)
+            if (g.base + kGuardBytes == p) { cudaFree(g.base); g.base = nullptr; return; }
+    }
+    cudaFree(p);
+}
 
 extern "C" {
 
@@ -163,29 +194,29 @@ static int engine_alloc(bk_engine *e) {
     const bk_hparams &hp = e->hp;
     const size_t T = (size_t)e->cap_tokens, d = hp.n_embd, f = hp.n_intermediate;
     for (int sl = 0; sl < 2; sl++) {
-        CK(cudaMalloc(&e->d_tokens2[sl], T * 4));
-        CK(cudaMalloc(&e->d_lens2[sl], (size_t)e->cap_seqs * 4));
-        CK(cudaMalloc(&e->d_out2[sl], (size_t)e->cap_seqs * d * 4));
+        CK(act_alloc(e, &e->d_tokens2[sl], T * 4));
+        CK(act_alloc(e, &e->d_lens2[sl], (size_t)e->cap_seqs * 4));
+        CK(act_alloc(e, &e->d_out2[sl], (size_t)e->cap_seqs * d * 4));
         CK(cudaMallocHost(&e->h_tokens2[sl], T * 4));
         CK(cudaMallocHost(&e->h_lens2[sl], (size_t)e->cap_seqs * 4));
         CK(cudaMallocHost(&e->h_out2[sl], (size_t)e->cap_seqs * d * 4));
         CK(cudaEventCreateWithFlags(&e->slot_done[sl], cudaEventDisableTiming));
     }
-    CK(cudaMalloc(&e->d_pos, T * 4));
-    CK(cudaMalloc(&e->d_tok, T * 4));
-    CK(cudaMalloc(&e->d_cu, ((size_t)e->cap_seqs + 1) * 4));
-    CK(cudaMalloc(&e->d_order, (size_t)e->cap_seqs * 4));
-    CK(cudaMalloc(&e->d_src_off, (size_t)e->cap_seqs * 4));
-    CK(cudaMalloc(&e->d_caller_off, (size_t)e->cap_seqs * 4));
-    CK(cudaMalloc(&e->x, T * d * 2));
-    CK(cudaMalloc(&e->qkv, T * 3 * d * 2));
-    CK(cudaMalloc(&e->att, T * d * 2));
-    CK(cudaMalloc(&e->pre, T * d * 2));
-    CK(cudaMalloc(&e->y, T * d * 2));
-    CK(cudaMalloc(&e->h, T * f * 2));
+    CK(act_alloc(e, &e->d_pos, T * 4));
+    CK(act_alloc(e, &e->d_tok, T * 4));
+    CK(act_alloc(e, &e->d_cu, ((size_t)e->cap_seqs + 1) * 4));
+    CK(act_alloc(e, &e->d_order, (size_t)e->cap_seqs * 4));
+    CK(act_alloc(e, &e->d_src_off, (size_t)e->cap_seqs * 4));
+    CK(act_alloc(e, &e->d_caller_off, (size_t)e->cap_seqs * 4));
+    CK(act_alloc(e, &e->x, T * d * 2));
+    CK(act_alloc(e, &e->qkv, T * 3 * d * 2));
+    CK(act_alloc(e, &e->att, T * d * 2));
+    CK(act_alloc(e, &e->pre, T * d * 2));
+    CK(act_alloc(e, &e->y, T * d * 2));
+    CK(act_alloc(e, &e->h, T * f * 2));
     if (e->qmode) {
-        CK(cudaMalloc(&e->xq, T * d * 2));
-        CK(cudaMalloc(&e->yq, T * d * 2));
+        CK(act_alloc(e, &e->xq, T * d * 2));
+        CK(act_alloc(e, &e->yq, T * d * 2));
     }
     // the GEMM A operand may read (never store) rows past T inside the last 128-row tile: keep them finite
     CK(cudaMemsetAsync(e->x, 0, T * d * 2, e->st));
@@ -225,6 +256,7 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     e->cap_seqs = cap_seqs;
     e->num_sms = prop.multiProcessorCount;
     e->qmode = hp->wtype == BK_Q4_0 ? 1 : hp->wtype == BK_Q4_1 ? 2 : 0;
+    if (const char *v = getenv("BERT_B200_GUARD")) e->guard_on = atoi(v) != 0;
     if (const char *v = getenv("BERT_B200_GRAPH_TOKENS")) e->graph_max_tokens = atoi(v);
     if (const char *v = getenv("BERT_B200_GRAPH_CACHE")) e->graph_cache = atoi(v) > 0 ? atoi(v) : 1;
     if (const char *v = getenv("BERT_B200_Q4_SMEM_TOKENS")) e->q4_smem_tokens = atoi(v);
@@ -248,7 +280,12 @@ BK_API void bk_engine_destroy(bk_engine *e) {
     void *bufs[] = {e->d_tokens2[0], e->d_tokens2[1], e->d_lens2[0], e->d_lens2[1], e->d_out2[0], e->d_out2[1], e->d_cu, e->d_pos, e->d_tok, e->d_order,
                     e->d_src_off, e->d_caller_off, e->x, e->xq, e->qkv,
                     e->att, e->pre, e->y, e->yq, e->h, e->hidden, e->sg_tokens, e->sg_lens, e->sg_out};
-    for (void *b : bufs) if (b) cudaFree(b);
+    void *staged[] = {e->hidden, e->sg_tokens, e->sg_lens, e->sg_out};  // plain allocations
+    for (void *b : bufs) {
+        bool plain = false;
+        for (void *q : staged) plain = plain || q == b;
+        if (plain) cudaFree(b); else act_free(e, b);
+    }
     for (int sl = 0; sl < 2; sl++) {
         if (e->h_tokens2[sl]) cudaFreeHost(e->h_tokens2[sl]);
         if (e->h_lens2[sl]) cudaFreeHost(e->h_lens2[sl]);
@@ -754,6 +791,30 @@ BK_API int bk_engine_read_hidden(bk_engine *e, int32_t which, float *out) {
 }
 
 BK_API int64_t bk_engine_launch_count(bk_engine *e) { return e ? e->launch_count : 0; }
+
+BK_API int64_t bk_engine_check_guards(bk_engine *e) {
+    if (!e) return -1;
+    if (!e->guard_on) { fail("engine was not created with BERT_B200_GUARD=1"); return -1; }
+    if (cudaSetDevice(e->device) != cudaSuccess || cudaStreamSynchronize(e->st) != cudaSuccess) { fail("guard check: stream error"); return -1; }
+    int64_t bad = 0;
+    std::vector<uint8_t> h(kGuardBytes);
+    for (const auto &g : e->guarded) {
+        if (!g.base) continue;
+        const size_t padded = (g.bytes + 255) & ~(size_t)255;
+        const uint8_t *parts[2] = {g.base, g.base + kGuardBytes + padded};
+        for (const uint8_t *part : parts) {
+            if (cudaMemcpy(h.data(), part, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) { fail("guard check: copy failed"); return -1; }
+            for (uint8_t b : h) bad += b != kGuardByte;
+        }
+        // the slack between the requested size and its 256-byte rounding belongs to the canary too
+        if (padded > g.bytes) {
+            std::vector<uint8_t> t(padded - g.bytes);
+            if (cudaMemcpy(t.data(), g.base + kGuardBytes + g.bytes, t.size(), cudaMemcpyDeviceToHost) != cudaSuccess) { fail("guard check: copy failed"); return -1; }
+            for (uint8_t b : t) bad += b != kGuardByte;
+        }
+    }
+    return bad;
+}
 
 BK_API int bk_profiler_range(int32_t on) {
     CK(on ? cudaProfilerStart() : cudaProfilerStop());

@@ -260,42 +260,159 @@ __device__ __forceinline__ void ln_store(float (&v)[NIT][8], int d, float eps, c
 }
 
 // ------------------------------------------------------------------------------- embed + LN
-template <bool kWriteQ, int NIT>
-__global__ void __launch_bounds__(256) embed_ln_kernel(const EmbedParams p) {
-    pdl_launch_dependents();
-    pdl_wait();
-    const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (t >= p.T) return;
-    const int lane = lane_id();
-    const int nch = p.d >> 3;
-    int tok = __ldg(p.tokens + t);
-    tok = min(max(tok, 0), p.n_vocab - 1);
-    const int ps = __ldg(p.pos + t);
-    float v[NIT][8];
+// The gather is latency bound, not byte bound (ncu r01e: DRAM 20 % busy, 25 warps resident, two dependent round trips per
+// token: id -> row): persistent warps walk over the tokens with the NEXT token's table rows already requested (raw bytes
+// held in registers) and the ids of the one after that on their way, so a warp always has a row in flight while it
+// normalises another.  The token-type row (always row 0, bert.cpp:871-872) is decoded once per CTA into shared memory.
+template <int WT, int NIT>
+struct RawRows {  // undecoded bytes of chunks lane, lane+32, .. of the word row and the position row
+    // F16: 16 B per chunk; Q4: scale word (d | m << 16) + the 8 bytes holding the chunk's nibbles; F32: not prefetched
+    uint4 w[WT == BK_F16 ? NIT : 1], p[WT == BK_F16 ? NIT : 1];
+    uint32_t wd[(WT == BK_Q4_0 || WT == BK_Q4_1) ? NIT : 1], pd[(WT == BK_Q4_0 || WT == BK_Q4_1) ? NIT : 1];
+    uint2 wq[(WT == BK_Q4_0 || WT == BK_Q4_1) ? NIT : 1], pq[(WT == BK_Q4_0 || WT == BK_Q4_1) ? NIT : 1];
+};
+template <int WT>
+__device__ __forceinline__ void q4_raw(const void *tab, int64_t r, int d, int c, uint32_t &dm, uint2 &qs) {
+    constexpr int bb = (WT == BK_Q4_0) ? 18 : 20;
+    const int blk = c >> 2, o = (c & 3) * 8;
+    const uint8_t *bp = reinterpret_cast<const uint8_t *>(tab) + (r * (d >> 5) + blk) * bb;
+    const uint16_t *hp = reinterpret_cast<const uint16_t *>(bp);  // blocks are 2-byte aligned
+    dm = __ldg(hp);
+    if (WT == BK_Q4_1) dm |= (uint32_t)__ldg(hp + 1) << 16;
+    const uint16_t *qp = reinterpret_cast<const uint16_t *>(bp + (bb - 16) + (o & 15));
+    qs.x = (uint32_t)__ldg(qp) | ((uint32_t)__ldg(qp + 1) << 16);
+    qs.y = (uint32_t)__ldg(qp + 2) | ((uint32_t)__ldg(qp + 3) << 16);
+}
+template <int WT>
+__device__ __forceinline__ void q4_decode8(uint32_t dm, uint2 qs, int c, float (&v)[8]) {
+    // element j < 16 of a block is the low nibble of byte j, element j + 16 the high nibble (ggml-quants.c:1074-1113)
+    const float dd = __half2float(__ushort_as_half((unsigned short)(dm & 0xFFFF)));
+    const float mm = (WT == BK_Q4_1) ? __half2float(__ushort_as_half((unsigned short)(dm >> 16))) : 0.f;
+    const int sh = ((c & 3) * 8 >= 16) ? 4 : 0;
+    const uint32_t w2[2] = {qs.x >> sh, qs.y >> sh};
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int q = (int)((w2[j >> 2] >> (8 * (j & 3))) & 0xF);
+        v[j] = (WT == BK_Q4_0) ? (float)(q - 8) * dd : (float)q * dd + mm;
+    }
+}
+template <int WT, int NIT>
+__device__ __forceinline__ void load_raw(const EmbedParams &p, int tok, int ps, int lane, int nch, RawRows<WT, NIT> &r) {
 #pragma unroll
     for (int it = 0; it < NIT; it++) {
         const int c = lane + 32 * it;
         if (c < nch) {
-            float w[8], ty[8], po[8];
-            load_row8(p.word, p.wtype, tok, p.d, c, w);
-            load_row8(p.type, p.wtype, 0, p.d, c, ty);   // token type is always 0 (bert.cpp:871-872)
-            load_row8(p.posw, p.wtype, ps, p.d, c, po);
-#pragma unroll
-            for (int j = 0; j < 8; j++) { const float a = ty[j] + w[j]; v[it][j] = po[j] + a; }  // (type + word) + pos, bert.cpp:880-887
+            if (WT == BK_F16) {
+                r.w[it] = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(p.word) + (int64_t)tok * p.d) + c);
+                r.p[it] = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(p.posw) + (int64_t)ps * p.d) + c);
+            } else if (WT == BK_Q4_0 || WT == BK_Q4_1) {
+                q4_raw<WT>(p.word, tok, p.d, c, r.wd[it], r.wq[it]);
+                q4_raw<WT>(p.posw, ps, p.d, c, r.pd[it], r.pq[it]);
+            }
         }
     }
-    ln_store<kWriteQ, NIT>(v, p.d, p.eps, p.gamma, p.beta, p.x + (size_t)t * p.d, kWriteQ ? p.xq + (size_t)t * p.d : nullptr, p.qmode);
+}
+template <int WT, bool kWriteQ, int NIT>
+__global__ void __launch_bounds__(256) embed_ln_kernel(const EmbedParams p) {
+    pdl_launch_dependents();
+    extern __shared__ float s_type[];  // [d] token-type row 0, decoded
+    const int lane = lane_id();
+    const int nch = p.d >> 3;
+    for (int c = threadIdx.x; c < nch; c += blockDim.x) {  // weights: independent of the previous kernel
+        float ty[8];
+        load_row8(p.type, WT, 0, p.d, c, ty);
+#pragma unroll
+        for (int j = 0; j < 8; j++) s_type[c * 8 + j] = ty[j];
+    }
+    pdl_wait();
+    __syncthreads();
+    const int wpg = gridDim.x * (blockDim.x >> 5);
+    int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (t >= p.T) return;
+    auto ids = [&](int tt, int &tok, int &ps) {
+        tok = __ldg(p.tokens + tt);
+        tok = min(max(tok, 0), p.n_vocab - 1);
+        ps = __ldg(p.pos + tt);
+    };
+    int tok, ps, tok_n = 0, ps_n = 0;
+    ids(t, tok, ps);
+    RawRows<WT, NIT> cur, nxt;
+    load_raw<WT, NIT>(p, tok, ps, lane, nch, cur);
+    int t_n = t + wpg;
+    if (t_n < p.T) ids(t_n, tok_n, ps_n);
+    for (;;) {
+        const bool more = t_n < p.T;
+        int tok_nn = 0, ps_nn = 0;
+        if (more) {
+            load_raw<WT, NIT>(p, tok_n, ps_n, lane, nch, nxt);   // next token's rows: in flight while this one is normalised
+            if (t_n + wpg < p.T) ids(t_n + wpg, tok_nn, ps_nn);
+        }
+        float v[NIT][8];
+#pragma unroll
+        for (int it = 0; it < NIT; it++) {
+            const int c = lane + 32 * it;
+            if (c < nch) {
+                float w[8], po[8];
+                if (WT == BK_F16) {
+                    float2 f;
+                    f = unpack_h2(cur.w[it].x); w[0] = f.x; w[1] = f.y; f = unpack_h2(cur.w[it].y); w[2] = f.x; w[3] = f.y;
+                    f = unpack_h2(cur.w[it].z); w[4] = f.x; w[5] = f.y; f = unpack_h2(cur.w[it].w); w[6] = f.x; w[7] = f.y;
+                    f = unpack_h2(cur.p[it].x); po[0] = f.x; po[1] = f.y; f = unpack_h2(cur.p[it].y); po[2] = f.x; po[3] = f.y;
+                    f = unpack_h2(cur.p[it].z); po[4] = f.x; po[5] = f.y; f = unpack_h2(cur.p[it].w); po[6] = f.x; po[7] = f.y;
+                } else if (WT == BK_Q4_0 || WT == BK_Q4_1) {
+                    q4_decode8<WT>(cur.wd[it], cur.wq[it], c, w);
+                    q4_decode8<WT>(cur.pd[it], cur.pq[it], c, po);
+                } else {
+                    load_row8(p.word, WT, tok, p.d, c, w);
+                    load_row8(p.posw, WT, ps, p.d, c, po);
+                }
+                const float4 t0 = *reinterpret_cast<const float4 *>(s_type + c * 8), t1 = *reinterpret_cast<const float4 *>(s_type + c * 8 + 4);
+                const float ty[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+#pragma unroll
+                for (int j = 0; j < 8; j++) { const float a = ty[j] + w[j]; v[it][j] = po[j] + a; }  // (type + word) + pos, bert.cpp:880-887
+            }
+        }
+        ln_store<kWriteQ, NIT>(v, p.d, p.eps, p.gamma, p.beta, p.x + (size_t)t * p.d, kWriteQ ? p.xq + (size_t)t * p.d : nullptr, p.qmode);
+        if (!more) break;
+        t = t_n; tok = tok_n; ps = ps_n;
+        t_n += wpg; tok_n = tok_nn; ps_n = ps_nn;
+        cur = nxt;
+    }
+}
+// resident CTAs of one instantiation on the current device (queried once): the persistent grid is exactly one wave
+template <int WT, bool Q, int NIT>
+static int embed_ln_resident(size_t smem) {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0, sms = 148, per = 1;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, embed_ln_kernel<WT, Q, NIT>, 256, smem) != cudaSuccess || per < 1) per = 1;
+        n = sms * per;
+    }
+    return n;
 }
 cudaError_t launch_embed_ln(const EmbedParams &p, cudaStream_t st) {
     if (p.d % 32 != 0 || p.d > kMaxChunks * 256) return cudaErrorInvalidValue;
     const int wpb = 8;
-    const int grid = (p.T + wpb - 1) / wpb;
+    const int want = (p.T + wpb - 1) / wpb;
     const int nit = (p.d + 255) / 256;  // 16-byte chunks per lane
-#define BK_EMBED(NIT)                                                        \
-    do {                                                                     \
-        LaunchConfig lc(dim3((unsigned)grid), dim3((unsigned)(wpb * 32)), 0, st);                          \
-        if (p.qmode) cudaLaunchKernelEx(&lc.cfg, embed_ln_kernel<true, NIT>, p);  \
-        else cudaLaunchKernelEx(&lc.cfg, embed_ln_kernel<false, NIT>, p);         \
+    const size_t smem = (size_t)p.d * sizeof(float);
+#define BK_EMBED_WT(WT_, NIT)                                                                          \
+    do { /* more tokens than one wave of warps: persistent warps, each walks over T / (grid * 8) tokens */ \
+        const int cap = p.qmode ? embed_ln_resident<WT_, true, NIT>(smem) : embed_ln_resident<WT_, false, NIT>(smem); \
+        LaunchConfig lc(dim3((unsigned)(want < cap ? want : cap)), dim3((unsigned)(wpb * 32)), smem, st); \
+        if (p.qmode) cudaLaunchKernelEx(&lc.cfg, embed_ln_kernel<WT_, true, NIT>, p);                  \
+        else cudaLaunchKernelEx(&lc.cfg, embed_ln_kernel<WT_, false, NIT>, p);                         \
+    } while (0)
+#define BK_EMBED(NIT)                                                                                  \
+    do {                                                                                               \
+        switch (p.wtype) {                                                                             \
+            case BK_F32: BK_EMBED_WT(BK_F32, NIT); break;                                              \
+            case BK_F16: BK_EMBED_WT(BK_F16, NIT); break;                                              \
+            case BK_Q4_0: BK_EMBED_WT(BK_Q4_0, NIT); break;                                            \
+            default: BK_EMBED_WT(BK_Q4_1, NIT); break;                                                 \
+        }                                                                                              \
     } while (0)
     if (nit <= 1) BK_EMBED(1);
     else if (nit == 2) BK_EMBED(2);
@@ -303,6 +420,7 @@ cudaError_t launch_embed_ln(const EmbedParams &p, cudaStream_t st) {
     else if (nit == 4) BK_EMBED(4);
     else BK_EMBED(kMaxChunks);
 #undef BK_EMBED
+#undef BK_EMBED_WT
     return cudaGetLastError();
 }
 
@@ -358,19 +476,20 @@ cudaError_t launch_add_ln(const __half *pre, const float *gamma, const float *be
 // ------------------------------------------------------------------------ mean-pool + L2 norm
 // One CTA per sentence.  e[k] = sum_t x[t][k] * (1/L) (the reference multiplies by a vector of 1/L,
 // bert.cpp:999-1001), out = e * (1/sqrt(sum e^2)) (bert.cpp:1004-1006).
-__global__ void __launch_bounds__(256) pool_norm_kernel(const __half *__restrict__ x, const int32_t *__restrict__ cu,
-                                                        const int32_t *__restrict__ order, int d, float *__restrict__ out) {
+__global__ void __launch_bounds__(512) pool_norm_kernel(const __half *__restrict__ x, const int32_t *__restrict__ cu,
+                                                         const int32_t *__restrict__ order, int d, float *__restrict__ out) {
     pdl_launch_dependents();
     pdl_wait();
     extern __shared__ float sacc[];  // [ngroups][d]
-    __shared__ float red[8];
+    __shared__ float red[32];
     const int s = blockIdx.x;
     const int t0 = __ldg(cu + s), t1 = __ldg(cu + s + 1);
     const int L = t1 - t0;
     const int nch = d >> 3;
-    // thread layout: column-chunk c = threadIdx.x % cpr, row group g = threadIdx.x / cpr
-    const int cpr = nch < 256 ? nch : 256;  // chunks handled per pass
-    const int groups = 256 / cpr > 0 ? 256 / cpr : 1;
+    const int nthr = (int)blockDim.x;
+    // thread layout: column-chunk c = threadIdx.x % cpr, row group g = threadIdx.x / cpr (the groups split the sentence's tokens)
+    const int cpr = nch < nthr ? nch : nthr;  // chunks handled per pass
+    const int groups = nthr / cpr > 0 ? nthr / cpr : 1;
     const int g = threadIdx.x / cpr, c0 = threadIdx.x % cpr;
     const float invL = 1.0f / (float)L;
     for (int c = c0; c < nch; c += cpr) {
@@ -401,19 +520,22 @@ __global__ void __launch_bounds__(256) pool_norm_kernel(const __half *__restrict
     if (lane_id() == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
     float tot = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; w++) tot += red[w];
+    for (int w = 0; w < (nthr >> 5); w++) tot += red[w];
     const float inv = 1.0f / sqrtf(tot);
     const int row = order ? __ldg(order + s) : s;  // the batcher's sorted position -> the caller's sentence index
     for (int k = threadIdx.x; k < d; k += blockDim.x) out[(size_t)row * d + k] = sacc[k] * inv;
 }
 cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, const int32_t *order, int n_seq, int d, float *out, cudaStream_t st) {
     if (d % 8 != 0) return cudaErrorInvalidValue;
+    // threads per sentence (a multiple of 32): the sentence's tokens are split over threads / (d / 8) row groups.
+    // BERT_B200_POOL_THREADS overrides (tuning); the summation order, hence the bits of the result, depend on it
+    static const int env_thr = [] { const char *v = getenv("BERT_B200_POOL_THREADS"); return v ? atoi(v) : 0; }();
+    int nthr = env_thr >= 32 && env_thr <= 512 ? (env_thr & ~31) : 512;  // measured on 512 sentences x 128 tokens: 256 threads 32 us, 512 threads 30 us
     const int nch = d >> 3;
-    const int cpr = nch < 256 ? nch : 256;
-    const int groups = 256 / cpr > 0 ? 256 / cpr : 1;
+    const int cpr = nch < nthr ? nch : nthr;
+    const int groups = nthr / cpr > 0 ? nthr / cpr : 1;
     const size_t smem = (size_t)groups * d * sizeof(float);
-    LaunchConfig lc(dim3((unsigned)n_seq), dim3(256), smem, st);
+    LaunchConfig lc(dim3((unsigned)n_seq), dim3((unsigned)nthr), smem, st);
     cudaLaunchKernelEx(&lc.cfg, pool_norm_kernel, x, cu_seqlens, order, d, out);
     return cudaGetLastError();
 }

@@ -99,6 +99,9 @@ BK_API int bk_engine_kernel_ms(bk_engine *e, float *ms, int32_t *launches);
 BK_API int bk_engine_read_hidden(bk_engine *e, int32_t which, float *out);
 BK_API int bk_engine_set_keep_hidden(bk_engine *e, int32_t on);
 BK_API int64_t bk_engine_launch_count(bk_engine *e); /* kernels launched since creation */
+/* engines created under BERT_B200_GUARD=1 carry a 4 KB canary on both sides of every activation / index buffer: the number of
+ * canary bytes overwritten so far (0 = no kernel wrote out of bounds), -1 on error.  Stand-in for compute-sanitizer memcheck. */
+BK_API int64_t bk_engine_check_guards(bk_engine *e);
 /* cudaProfilerStart (on=1) / cudaProfilerStop (on=0): lets `ncu --profile-from-start off` see only the timed region */
 BK_API int bk_profiler_range(int32_t on);
 

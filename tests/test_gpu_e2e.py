@@ -281,3 +281,23 @@ def test_large_batch_properties(binding, make_model):
     out2 = m.eval_batch([batch[i] for i in perm])
     assert np.array_equal(out2, out[perm])
     m.close()
+
+
+@pytest.mark.parametrize("ftype", ["f16", "q4_0", "q4_1"])
+@pytest.mark.parametrize("fused", ["-1", "0"])
+def test_no_kernel_writes_out_of_bounds(ftype, fused, binding, make_model, monkeypatch):
+    """compute-sanitizer is closed on the GPU pool (profiles/r02_sanitize_memcheck.log), so the bounds check is the engine's own:
+    under BERT_B200_GUARD=1 every activation / index buffer sits between two 4 KB canaries, and after ragged batches through
+    every kernel of the path (three attention kernels, GEMM + add_ln and the fused cluster kernel, packed-Q4 GEMM, batcher,
+    graph replay) no canary byte may have changed.  Capacity = exactly one 256-row tile multiple, so a store one row past the
+    buffers would land in a canary."""
+    monkeypatch.setenv("BERT_B200_GUARD", "1")
+    monkeypatch.setenv("BERT_B200_FUSED_LN_TOKENS", fused)
+    path = make_model("mini384", ftype, seed=61)
+    e = binding.Engine(path, cap_tokens=1536, cap_seqs=64)
+    rng = np.random.default_rng(23)
+    for lens in ([1, 5, 17, 48], [512, 512, 511], [1, 33, 100, 128, 129, 300, 512, 64, 3, 2], [128] * 12, [7] * 64, [1536 // 3] * 3, [1]):
+        out = e.forward([rand_tokens(rng, 500, L) for L in lens])
+        assert np.allclose(np.linalg.norm(out, axis=1), 1.0, atol=1e-3)
+    assert e.check_guards() == 0
+    e.close()
