@@ -7,7 +7,7 @@ NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-fvisibility=hidd
 CXXFLAGS  := -O2 -std=c++17 -fPIC -fvisibility=hidden -Wall -Wextra -Wno-unused-parameter -I/usr/local/cuda/include
 SRC       := embedding.cpp_b200/csrc
 OBJ       := build/obj
-CU_SRCS   := gemm_tcgen05.cu gemm_ln.cu rowwise.cu attention_tc.cu engine.cu test_entry.cu
+CU_SRCS   := gemm_tcgen05.cu gemm_ws.cu gemm_ln.cu rowwise.cu attention_tc.cu engine.cu test_entry.cu
 CPP_SRCS  := api.cpp gguf.cpp tokenizer_wp.cpp quantize.cpp
 OBJS      := $(addprefix $(OBJ)/,$(CU_SRCS:.cu=.o) $(CPP_SRCS:.cpp=.o))
 
@@ -17,7 +17,7 @@ build/libbert.so: $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -cudart static -lpthread -ldl -lrt
 	ln -sf libbert.so build/libbert_shared.so
 
-$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/attention_persist.cuh $(SRC)/attention_stream.cuh $(SRC)/kernels.h include/bk_api.h | $(OBJ)
+$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/gemm_parts.cuh $(SRC)/attention_persist.cuh $(SRC)/attention_stream.cuh $(SRC)/kernels.h include/bk_api.h | $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(OBJ)/$*.ptxas.log || (cat $(OBJ)/$*.ptxas.log; false)
 
 $(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/gguf.h $(SRC)/tokenizer_wp.h include/bert.h include/bk_api.h | $(OBJ)

@@ -358,7 +358,7 @@ static cudaError_t launch_att_stream(const CUtensorMap &tm, const int32_t *cu, i
     const int Lk64 = (max_len + 63) & ~63;
     // a shorter sentence inside a longer launch finds its second exchange buffer in the K / V space it does not use
     const size_t smem = (size_t)kStreamQ * kAttQ * DH * 2 + 4 * kAttQ * 128 + (size_t)2 * Lk64 * DH * 2 + kStreamTail + (Lk64 <= 256 ? 2 : 1) * 2048;
-    static bool attr_set[64] = {false};
+    static std::atomic<bool> attr_set[64];
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {

@@ -22,6 +22,7 @@
 // 32-key slice), warp 4G is the control warp (TMA, MMA issue, TMEM allocation).  G = 1/2/4 for
 // Lk <= 128/256/512 so a CTA always has one softmax warp per 32 rows x 128 keys.
 #include <cmath>
+#include <atomic>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -401,7 +402,7 @@ static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_se
     const size_t body = multi ? (size_t)2 * kAttQ * DH * 2 + 4 * kAttQ * 128 + (size_t)2 * Lk64 * DH * 2
                               : (size_t)(qk > 2 * kAttQ * 128 ? qk : 2 * kAttQ * 128) + (size_t)Lk64 * DH * 2;
     const size_t smem = body + 256 /*barriers*/ + (size_t)G * 128 * 4 + 512 /*ones tile*/;
-    static bool attr_set[64] = {false};  // per kernel instance and device (the attribute is per device)
+    static std::atomic<bool> attr_set[64];  // per kernel instance and device (the attribute is per device)
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {

@@ -135,6 +135,12 @@ struct bk_engine {
     // only Q4 bytes cross HBM: weight traffic dominates there); larger ones use the f16 operand copies, where
     // weights are < 2% of the bytes moved and the decode would compete with the epilogue for issue slots.
     int q4_smem_tokens = 1024;    // BERT_B200_Q4_SMEM_TOKENS; -1 = always, 0 = never
+    // BERT_B200_Q4_WS=1 (Q4 models): QKV and FFN-up (K = n_embd <= 1024) run weight-stationary from the packed blocks at every batch
+    // size above the latency regime (gemm_ws.cu: every CTA pair decodes its column tile once) and have NO f16 operand copy --
+    // the packed GGUF blocks are the only copy of those weights in HBM.  Costs 10-25 % on those two GEMMs (the resident slice
+    // takes the shared memory that hides latency), so the default keeps f16 operand copies for batches above q4_smem_tokens.
+    // Attention-output and FFN-down run in the fused projection + LayerNorm kernel from f16 copies either way.
+    bool q4_ws = false;
     // batches of more than this many tokens run attention-output and FFN-down as ONE kernel each with the residual add and
     // the LayerNorm in the GEMM epilogue (gemm_ln.cu: a cluster per 256-row block); smaller ones have too few row blocks to
     // fill the clusters and use GEMM(+bias+residual) followed by add_ln.  BERT_B200_FUSED_LN_TOKENS; -1 = never
@@ -261,6 +267,11 @@ BK_API bk_engine *bk_engine_create(int device, const bk_hparams *hp, int32_t cap
     if (const char *v = getenv("BERT_B200_GRAPH_CACHE")) e->graph_cache = atoi(v) > 0 ? atoi(v) : 1;
     if (const char *v = getenv("BERT_B200_Q4_SMEM_TOKENS")) e->q4_smem_tokens = atoi(v);
     if (const char *v = getenv("BERT_B200_FUSED_LN_TOKENS")) e->fused_ln_tokens = atoi(v);
+    {
+        const char *v = getenv("BERT_B200_Q4_WS");
+        e->q4_ws = e->qmode != 0 && v && atoi(v) != 0 && gemm_ws_supported(3 * hp->n_embd, hp->n_embd, e->num_sms) &&
+                   gemm_ws_supported(hp->n_intermediate, hp->n_embd, e->num_sms);
+    }
     e->tens.resize(5 + 16 * (size_t)hp->n_layer);
     e->layers.resize(hp->n_layer);
     if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess) { fail("cudaStreamCreate failed"); delete e; return nullptr; }
@@ -346,15 +357,16 @@ BK_API int bk_engine_finalize(bk_engine *e) {
         if (expect(e, L_SLOT(l, S_W2), f, d, false, "output.dense.weight")) return -1;
         if (expect(e, L_SLOT(l, S_B2), d, 1, true, "output.dense.bias")) return -1;
 
-        CK(cudaMalloc(&L.wqkv, (size_t)3 * d * d * 2));
+        const bool ws = e->q4_ws;  // QKV and FFN-up have no f16 operand copy: they always run from the packed blocks
+        if (!ws) CK(cudaMalloc(&L.wqkv, (size_t)3 * d * d * 2));
         CK(cudaMalloc(&L.wo, (size_t)d * d * 2));
-        CK(cudaMalloc(&L.w1, (size_t)f * d * 2));
+        if (!ws) CK(cudaMalloc(&L.w1, (size_t)f * d * 2));
         CK(cudaMalloc(&L.w2, (size_t)d * f * 2));
         CK(cudaMalloc(&L.bqkv, (size_t)3 * d * 4));
         const int qkvw[3] = {S_QW, S_KW, S_VW}, qkvb[3] = {S_QB, S_KB, S_VB};
         for (int i = 0; i < 3; i++) {
             const HostTensor &w = e->tens[L_SLOT(l, qkvw[i])];
-            CK(launch_weight_to_f16(w.dev, w.type, d, d, L.wqkv + (size_t)i * d * d, e->st));
+            if (!ws) CK(launch_weight_to_f16(w.dev, w.type, d, d, L.wqkv + (size_t)i * d * d, e->st));
             CK(cudaMemcpyAsync(L.bqkv + (size_t)i * d, e->tens[L_SLOT(l, qkvb[i])].dev, (size_t)d * 4, cudaMemcpyDeviceToDevice, e->st));
         }
         if (e->qmode) {
@@ -379,7 +391,7 @@ BK_API int bk_engine_finalize(bk_engine *e) {
             }
         }
         { const HostTensor &w = e->tens[L_SLOT(l, S_OW)]; CK(launch_weight_to_f16(w.dev, w.type, d, d, L.wo, e->st)); }
-        { const HostTensor &w = e->tens[L_SLOT(l, S_W1)]; CK(launch_weight_to_f16(w.dev, w.type, f, d, L.w1, e->st)); }
+        if (!ws) { const HostTensor &w = e->tens[L_SLOT(l, S_W1)]; CK(launch_weight_to_f16(w.dev, w.type, f, d, L.w1, e->st)); }
         { const HostTensor &w = e->tens[L_SLOT(l, S_W2)]; CK(launch_weight_to_f16(w.dev, w.type, d, f, L.w2, e->st)); }
         L.bo = (const float *)e->tens[L_SLOT(l, S_OB)].dev;
         L.b1 = (const float *)e->tens[L_SLOT(l, S_B1)].dev;
@@ -388,8 +400,12 @@ BK_API int bk_engine_finalize(bk_engine *e) {
         L.ln1b = (const float *)e->tens[L_SLOT(l, S_LN1B)].dev;
         L.ln2g = (const float *)e->tens[L_SLOT(l, S_LN2G)].dev;
         L.ln2b = (const float *)e->tens[L_SLOT(l, S_LN2B)].dev;
-        bool ok = make_weight_maps(&L.tm_wqkv, L.wqkv, 3 * (int)d, (int)d) && make_weight_maps(&L.tm_wo, L.wo, (int)d, (int)d) &&
-                  make_weight_maps(&L.tm_w1, L.w1, (int)f, (int)d) && make_weight_maps(&L.tm_w2, L.w2, (int)d, (int)f);
+        bool ok = make_weight_maps(&L.tm_wo, L.wo, (int)d, (int)d) && make_weight_maps(&L.tm_w2, L.w2, (int)d, (int)f);
+        if (!ws) ok = ok && make_weight_maps(&L.tm_wqkv, L.wqkv, 3 * (int)d, (int)d) && make_weight_maps(&L.tm_w1, L.w1, (int)f, (int)d);
+        else {  // shape only: the packed kernels take no weight tensor map (an A-operand map stands in as the unused argument)
+            for (int i = 0; i < 6; i++) { L.tm_wqkv.tm[i] = L.tm_wo.tm[i]; L.tm_w1.tm[i] = L.tm_wo.tm[i]; }
+            L.tm_wqkv.N = 3 * (int)d; L.tm_wqkv.K = (int)d; L.tm_w1.N = (int)f; L.tm_w1.K = (int)d;
+        }
         if (!ok) return fail("cuTensorMapEncodeTiled failed for layer %d weights", l);
     }
     CK(cudaStreamSynchronize(e->st));
@@ -444,7 +460,13 @@ int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const WeightMaps &W
     KTimer t(e, kind);
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.bias = bias; p.epi = epi;
-    if (e->qmode && packed && K % 64 == 0 && (e->q4_smem_tokens < 0 || M <= e->q4_smem_tokens)) { p.wq = packed; p.wq_type = e->hp.wtype; }
+    const bool ws_kind = e->q4_ws && (kind == BK_K_GEMM_QKV || kind == BK_K_GEMM_FF1);  // no f16 copy exists for these
+    if (e->qmode && packed && K % 64 == 0 && (e->q4_smem_tokens < 0 || M <= e->q4_smem_tokens || ws_kind)) { p.wq = packed; p.wq_type = e->hp.wtype; }
+    if (ws_kind && !(e->q4_smem_tokens < 0 || M <= e->q4_smem_tokens)) {
+        CK(launch_gemm_ws(tmA, tmOut, p, e->num_sms, e->st));  // weight-stationary: decode once per CTA pair
+        e->launch_count++;
+        return 0;
+    }
     CK(launch_gemm(tmA, W, tmOut, tmRes, p, e->num_sms, e->st));
     e->launch_count++;
     return 0;

@@ -67,6 +67,13 @@ bool make_tmap_f16_2d(CUtensorMap *tm, const void *base, uint64_t inner, uint64_
 // y[i] = the epilogue's GELU of x[i] (tests)
 cudaError_t launch_gelu_test(const float *x, float *y, int n, cudaStream_t st);
 
+// ---- gemm_ws.cu -----------------------------------------------------------------------------
+// weight-stationary Q4 GEMM: p.wq = the re-tiled packed blocks (launch_q4_retile), the ONLY copy of the weight; every CTA pair decodes
+// its column tile (256 / 192 / 128 wide: what its resident slice leaves room for) once into shared memory and streams all row tiles
+// past it.  K % 64 == 0, the slice of the narrowest tile that divides N must fit (K <= 1024 at 128 columns), no residual.
+bool gemm_ws_supported(int N, int K, int num_sms);
+cudaError_t launch_gemm_ws(const CUtensorMap &tmA, const CUtensorMap &tmOut, const GemmParams &p, int num_sms, cudaStream_t st, int force_bn = 0);
+
 // ---- gemm_ln.cu -----------------------------------------------------------------------------
 // y = LN(A . W^T + bias + resid) * gamma + beta (and its Q8-rounded copy yq when qmode != 0) in one kernel:
 // clusters of CTA pairs hold whole 256 x N row blocks in TMEM.  N must be 384, 768 or 1024.

@@ -69,7 +69,8 @@ BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint1
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.bias = dB.as<float>(); p.epi = epi;
     const int bn = (epi >> 8) & 0xFFF, cg = (epi >> 20) & 0xF;  // tests may force the tile: epi | (BN << 8) | (CG << 20)
-    const bool in_smem = (epi >> 28) & 1;                         // ... and, for Q4 weights, the in-smem decode path
+    const bool ws = (epi >> 29) & 1;                              // ... the weight-stationary kernel (gemm_ws.cu; Q4 weights, K <= 1024)
+    const bool in_smem = ((epi >> 28) & 1) || ws;                 // ... and, for Q4 weights, the in-smem decode path
     p.epi = epi & 0xFF;
     DevBuf dWt;
     if (in_smem) {
@@ -80,11 +81,15 @@ BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint1
     }
     cudaEvent_t a, b;
     TCK(cudaEventCreate(&a)); TCK(cudaEventCreate(&b));
-    TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn, cg));  // warm-up (also first-use setup)
+    auto run = [&]() -> cudaError_t {
+        if (ws) return launch_gemm_ws(tmA, tmO, p, prop.multiProcessorCount, 0, bn);
+        return launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn, cg);
+    };
+    TCK(run());  // warm-up (also first-use setup)
     TCK(cudaDeviceSynchronize());
     const int reps = ms ? 5 : 1;
     TCK(cudaEventRecord(a, 0));
-    for (int i = 0; i < reps; i++) TCK(launch_gemm(tmA, wm, tmO, resid ? &tmR : nullptr, p, prop.multiProcessorCount, 0, bn, cg));
+    for (int i = 0; i < reps; i++) TCK(run());
     TCK(cudaEventRecord(b, 0));
     TCK(cudaDeviceSynchronize());
     float t = 0;

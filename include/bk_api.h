@@ -112,7 +112,8 @@ enum { BK_EPI_BIAS = 0, BK_EPI_BIAS_RESID = 1, BK_EPI_BIAS_GELU = 2, BK_EPI_BIAS
  * ggml.c:9388-9597, bert.cpp:909-910.  wtype selects how W is stored (BK_F16 raw halves,
  * BK_Q4_0/BK_Q4_1 GGUF blocks along K, BK_F32 floats).  epi may carry a forced tile width in bits 8..:
  * epi | (BN << 8) | (CG << 20), BN in {64,128,192,256}, CG in {1,2} CTAs per tile (0 = automatic choice);
- * bit 28 set with Q4 weights: W stays packed in device memory and is decoded in shared memory by the GEMM. */
+ * bit 28 set with Q4 weights: W stays packed in device memory and is decoded in shared memory by the GEMM (per K stage);
+ * bit 29: the weight-stationary kernel (gemm_ws.cu: each CTA pair decodes its column tile once; K <= 1024, N % 128 == 0). */
 BK_API int bk_test_gemm(int device, int32_t M, int32_t N, int32_t K, const uint16_t *A, const void *W,
                         int32_t wtype, const float *bias, const uint16_t *resid, int32_t epi,
                         uint16_t *out, float *ms);

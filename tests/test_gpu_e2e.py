@@ -301,3 +301,21 @@ def test_no_kernel_writes_out_of_bounds(ftype, fused, binding, make_model, monke
         assert np.allclose(np.linalg.norm(out, axis=1), 1.0, atol=1e-3)
     assert e.check_guards() == 0
     e.close()
+
+
+@pytest.mark.parametrize("ftype", ["q4_0", "q4_1"])
+@pytest.mark.parametrize("shape", ["mini384", "bert-base"])
+def test_q4_weight_stationary_engine_equals_default(shape, ftype, binding, make_model, monkeypatch):
+    """BERT_B200_Q4_WS=1: QKV and FFN-up run weight-stationary from the packed GGUF blocks (gemm_ws.cu) and no f16 copy of those
+    weights exists; the embeddings must equal the default engine's (f16 operand copies above 1024 tokens) bit for bit"""
+    path = make_model(shape, ftype, seed=71, n_vocab=600)
+    rng = np.random.default_rng(29)
+    batch = [rand_tokens(rng, 600, int(L)) for L in [512, 300, 129, 128, 64, 33, 2, 1] + [128] * 16 + list(rng.integers(1, 400, 24))]   # > 4096 tokens
+    outs = []
+    for ws in ("0", "1"):
+        monkeypatch.setenv("BERT_B200_Q4_WS", ws)
+        m = binding.BertB200(path)
+        outs.append((m.eval_batch(batch), m.eval_batch(batch[:9]), m.eval(batch[3])))   # fused-LN regime, 1024..4096 tokens, one sentence
+        m.close()
+    for a, b in zip(outs[0], outs[1]):
+        assert np.array_equal(a, b)

@@ -138,6 +138,33 @@ def test_gemm_q4_decoded_in_shared_memory(lib, gio, wname, wtype, M, N, K, epi):
         assert (err <= 2e-3 * np.abs(ref) + 2e-3).all(), float(err.max())
 
 
+@pytest.mark.parametrize("wname,wtype", [("q4_0", 2), ("q4_1", 3)])
+@pytest.mark.parametrize("M,N,K,epi", [(1000, 2304, 768, 0), (300, 3072, 768, 2), (5000, 1152, 384, 0), (777, 3072, 1024, 3), (129, 128, 64, 0),
+                                       (1, 256, 128, 2), (20000, 2304, 768, 0), (4096, 4096, 1024, 4), (257, 1536, 384, 3)])
+def test_gemm_q4_weight_stationary(lib, gio, wname, wtype, M, N, K, epi):
+    """gemm_ws.cu: the packed GGUF blocks are the only copy of W; every CTA pair decodes its 128-column tile once into shared
+    memory and streams all row tiles past it (QKV and FFN-up of Q4 models above the latency regime).  Must equal, bit for bit,
+    the kernel fed from the f16 copy expanded at load (same decoder values, same MMA K order, same epilogue arithmetic) --
+    every epilogue these projections use: bias, bias + GELU, bias + GELU + Q8_0 / Q8_1 rounding."""
+    rng = np.random.default_rng(M + N + K + wtype + epi)
+    A = h(rng.standard_normal((M, K)) * 0.5)
+    Wf = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    raw = np.ascontiguousarray((gio.quantize_q4_0 if wtype == 2 else gio.quantize_q4_1)(Wf))
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float32)
+    at_load, _ = run_gemm(lib, A, raw, wtype, N, bias, None, epi)
+    # the automatic tile width and every width whose resident slice fits: (227 KB - 34.5 KB of boxes / barriers - 3 A stages) of smem
+    widths = [0] + [bn for bn in (128, 192, 256) if N % bn == 0 and (K // 64) * (bn // 2) * 128 <= 227 * 1024 - 34304 - 3 * 16384 and 74 // (N // bn) >= 1]
+    assert len(widths) >= 2
+    for bn in widths:
+        ws, _ = run_gemm(lib, A, raw, wtype, N, bias, None, epi | (1 << 29) | (bn << 8))
+        assert np.array_equal(at_load.view(np.uint16), ws.view(np.uint16)), (bn, int((at_load.view(np.uint16) != ws.view(np.uint16)).sum()))
+    if epi == 0:
+        Wd = gio.dequantize(raw, wtype, (N, K)).astype(np.float16).astype(np.float32)
+        ref = A.astype(np.float32) @ Wd.T + bias
+        err = np.abs(ws.astype(np.float32) - ref)
+        assert (err <= 2e-3 * np.abs(ref) + 2e-3).all(), float(err.max())
+
+
 @pytest.mark.parametrize("qepi,fn", [(3, "oracle_quant_q8_0_roundtrip"), (4, "oracle_quant_q8_1_roundtrip")])
 def test_gemm_gelu_q8_epilogue(lib, binding, orc, make_model, qepi, fn):
     M, N, K = 256, 512, 128
