@@ -659,6 +659,12 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
     return 0;
 }
 
+// BERT_B200_PDL_ALL=1: programmatic dependent launch between the kernels of large batches too (default: the latency path only)
+static bool pdl_all() {
+    static const bool on = [] { const char *v = getenv("BERT_B200_PDL_ALL"); return v && atoi(v) != 0; }();
+    return on;
+}
+
 // ids and lengths of the batch are in the slot's pinned staging buffers: upload, all kernels, download into host_out (pinned, or
 // the slot's own buffer when null)
 static int enqueue_slot(bk_engine *e, int slot, int T, int n_seq, int mx, float *host_out) {
@@ -679,7 +685,12 @@ static int enqueue_slot(bk_engine *e, int slot, int T, int n_seq, int mx, float 
         if (ran == 0) ran = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot]) ? -1 : 1;
         pdl_flag() = false;
         if (ran < 0) return -1;
-    } else if (forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot])) return -1;
+    } else {
+        pdl_flag() = use_pdl && pdl_all();
+        const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot]);
+        pdl_flag() = false;
+        if (rc) return -1;
+    }
     float *dst = host_out ? host_out : e->h_out2[slot];
     CK(cudaMemcpyAsync(dst, e->d_out2[slot], (size_t)n_seq * e->hp.n_embd * 4, cudaMemcpyDeviceToHost, e->st));
     CK(cudaEventRecord(e->slot_done[slot], e->st));
@@ -754,6 +765,7 @@ BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernel
     e->timing = time_kernels != 0;
     CK(cudaEventRecord(a, e->st));
     int rc = 0;
+    pdl_flag() = pdl_all() && !e->timing;
     for (int i = 0; i < iters && rc == 0; i++)
         for (const auto &sl : e->slices) {
             e->st_T = sl.T; e->st_nseq = sl.n_seq; e->st_maxlen = sl.max_len;
@@ -762,6 +774,7 @@ BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernel
             if (rc) break;
         }
     e->timing = false;
+    pdl_flag() = false;
     if (rc) { cudaEventDestroy(a); cudaEventDestroy(b); return rc; }
     CK(cudaEventRecord(b, e->st));
     CK(cudaStreamSynchronize(e->st));

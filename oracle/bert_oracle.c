@@ -16,7 +16,7 @@
  *                                                         ggml.c:757-790,1163-1234
  *     - LayerNorm / sum / softmax denominators in double ggml.c:8976-9004,10536-10558
  *
- * Parity pin: tests/test_oracle_vs_ref.py runs this file against
+ * Parity pin: tests/test_oracle.py runs this file against
  * oracle/_ref/libbert_ref.so (the reference's own sources compiled here, see
  * oracle/build_ref.sh) on the same GGUF files and token ids; the reference
  * ships no golden embedding vectors (examples/test_embedding.cpp only prints).
