@@ -17,7 +17,7 @@ build/libbert.so: $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -cudart static -lpthread -ldl -lrt
 	ln -sf libbert.so build/libbert_shared.so
 
-$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/gemm_parts.cuh $(SRC)/attention_persist.cuh $(SRC)/attention_stream.cuh $(SRC)/kernels.h include/bk_api.h | $(OBJ)
+$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/gemm_parts.cuh $(SRC)/attention_persist.cuh $(SRC)/attention_loop.cuh $(SRC)/attention_stream.cuh $(SRC)/kernels.h include/bk_api.h | $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(OBJ)/$*.ptxas.log || (cat $(OBJ)/$*.ptxas.log; false)
 
 $(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/gguf.h $(SRC)/tokenizer_wp.h include/bert.h include/bk_api.h | $(OBJ)

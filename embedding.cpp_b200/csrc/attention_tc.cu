@@ -31,6 +31,7 @@
 namespace bk {
 
 constexpr int kAttQ = 128;  // queries per CTA
+constexpr bool kAttLoopDefault = true;   // attention_loop.cuh for launches of sentences <= 128 tokens (A/B: BERT_B200_ATT_LOOP)
 
 // K-major operand tile whose rows are ROWB = 64 or 128 bytes (dh = 32 / 64 halves): TMA SWIZZLE_64B / 128B
 template <int ROWB>
@@ -391,6 +392,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
 }
 
 #include "attention_persist.cuh"
+#include "attention_loop.cuh"
 #include "attention_stream.cuh"
 
 template <int DH, int G>
@@ -424,15 +426,22 @@ cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens
     static const int env_g = [] { const char *v = getenv("BERT_B200_ATT_G"); return v ? atoi(v) : 0; }();
     int G = max_len <= 128 ? 1 : max_len <= 256 ? 2 : 4;
     if (env_g == 1 || env_g == 2 || env_g == 4) G = env_g;
-    // launches of short sentences (<= BERT_B200_ATT_PERSIST tokens, default 48; 0 = never, 128 = whenever possible): persistent
-    // CTAs with two items in flight.  One CTA per item spends most of its life on set-up and load latency when a sentence
-    // is a few rows of a 128-row tile (measured on 65 536 tokens: 16-token sentences 379 -> 342 us, 32: 200 -> 174 us); from
-    // 64 tokens on, four independent CTAs per SM hide that better than two persistent ones (64: 122 vs 129 us, 128: 103 vs 119 us)
-    const char *pv = getenv("BERT_B200_ATT_PERSIST");  // read per launch: the tests switch it inside one process
-    const int persist_max = pv ? atoi(pv) : 48;
+    // launches whose longest sentence has <= 128 tokens: the per-item kernel with the CTA kept on its SM, four per SM, each walking over
+    // items (attention_loop.cuh).  Per 65 536 tokens of BERT-base F16 (tools/att_len_probe.py), loop / persistent two-stage / one CTA
+    // per item: L = 16: 286 / 378 / 529 us, 32: 169 / 204 / 295, 48: 148 / 203 / 229, 64: 122 / 178 / 184, 96: 129 / - / 171,
+    // 128: 128 / - / 138 (Q4_0: 379 / 504 / 527 at 16, 137 / - / 188 at 64, 136 / - / 137 at 128).
+    // BERT_B200_ATT_LOOP=0: one CTA per (sentence, head); BERT_B200_ATT_PERSIST=n: the persistent two-stage kernel
+    // (attention_persist.cuh) for launches up to n tokens -- both kept for the A/B tests, read per launch.
+    const char *pv = getenv("BERT_B200_ATT_PERSIST");
+    const int persist_max = pv ? atoi(pv) : 0;
     if (max_len <= kAttQ && max_len <= persist_max && env_g == 0) {
         if (dh == 64) return launch_att_persist<64>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
         if (dh == 32) return launch_att_persist<32>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
+    }
+    const char *lv = getenv("BERT_B200_ATT_LOOP");
+    if (max_len <= kAttQ && env_g == 0 && (lv ? atoi(lv) != 0 : kAttLoopDefault)) {
+        if (dh == 64) return launch_att_loop<64>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
+        if (dh == 32) return launch_att_loop<32>(tmQKV, cu_seqlens, n_seq, d, n_head, out, qmode, st);
     }
     // launches with sentences of more than 128 tokens: scores streamed through a TMEM ring (BERT_B200_ATT_STREAM=0: whole
     // score block resident, attention_tc_kernel)

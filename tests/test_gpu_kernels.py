@@ -282,12 +282,14 @@ def test_attention_persistent_kernel(lib, orc, make_model, monkeypatch, d, H, n_
     qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
     L = np.array(lens, np.int32)
     outs = []
-    for persist in ("128", "0"):
+    for persist, loop in (("128", "1"), ("0", "0"), ("0", "1")):   # persistent two-stage | one CTA per item | looping CTAs (default)
         monkeypatch.setenv("BERT_B200_ATT_PERSIST", persist)
+        monkeypatch.setenv("BERT_B200_ATT_LOOP", loop)
         out = np.zeros((T, d), np.float16)
         assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(out)) == 0
         outs.append(out)
     assert np.array_equal(outs[0].view(np.uint16), outs[1].view(np.uint16))
+    assert np.array_equal(outs[2].view(np.uint16), outs[1].view(np.uint16))
     if qmode == 0:
         o = orc.Oracle(make_model("tiny", "f32", 13, 300))
         off = 0
@@ -405,3 +407,24 @@ def test_embed_ln(lib, binding, gio, orc, make_model, shape, ftype):
         flips = int((errq > 1e-3 * np.abs(rt) + 1e-6).sum())
         print(f"\nembed_ln {shape} {ftype}: {flips} of {errq.size} Q8 roundings flipped by one step")
         assert flips <= 0.002 * errq.size and (errq <= step * 1.01 + 1e-3).all()
+
+
+@pytest.mark.parametrize("d,H,n_seq,qmode", [(768, 12, 700, 0), (768, 12, 100, 1), (128, 4, 3000, 0), (1024, 16, 64, 2), (256, 4, 13, 0)])
+def test_attention_loop_kernel(lib, monkeypatch, d, H, n_seq, qmode):
+    """attention_loop.cuh: the per-item kernel with the CTA kept on its SM (four per SM, each walking over several
+    (sentence, head) items; the next item's loads requested when the current P.V MMAs retire).  More items than CTAs, fewer
+    items than CTAs, every key-chunk / slice boundary: bit for bit the one-CTA-per-item kernel."""
+    rng = np.random.default_rng(d + n_seq + qmode)
+    lens = [1, 15, 16, 17, 32, 33, 63, 64, 65, 96, 97, 127, 128] + [int(v) for v in rng.integers(1, 129, n_seq - 13)]
+    lens = [lens[i] for i in rng.permutation(len(lens))]
+    T = sum(lens)
+    qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
+    L = np.array(lens, np.int32)
+    monkeypatch.setenv("BERT_B200_ATT_PERSIST", "0")
+    outs = []
+    for loop in ("1", "0"):
+        monkeypatch.setenv("BERT_B200_ATT_LOOP", loop)
+        out = np.zeros((T, d), np.float16)
+        assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(out)) == 0
+        outs.append(out)
+    assert np.array_equal(outs[0].view(np.uint16), outs[1].view(np.uint16)), int((outs[0].view(np.uint16) != outs[1].view(np.uint16)).sum())
