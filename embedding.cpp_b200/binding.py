@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(ROOT, "build", "libbert.so")
+LIB_PATH = os.environ.get("BERT_B200_LIB") or os.path.join(ROOT, "build", "libbert.so")   # BERT_B200_LIB: another build of the library (A/B of compile-time knobs)
 
 _i32p = ctypes.POINTER(ctypes.c_int32)
 _f32p = ctypes.POINTER(ctypes.c_float)

@@ -191,8 +191,8 @@ __device__ __forceinline__ void load_row8(const void *tab, int wtype, int64_t r,
         for (int j = 0; j < 4; j++) {
             const uint32_t w = __ldg(qp + j);
             const int q0 = (w >> sh) & 0xF, q1 = (w >> (8 + sh)) & 0xF;
-            if (wtype == BK_Q4_0) { v[2 * j] = (float)(q0 - 8) * dd; v[2 * j + 1] = (float)(q1 - 8) * dd; }
-            else { v[2 * j] = (float)q0 * dd + mm; v[2 * j + 1] = (float)q1 * dd + mm; }
+            if (wtype == BK_Q4_0) { v[2 * j] = __fmul_rn(small_int_to_float(q0, 8.f), dd); v[2 * j + 1] = __fmul_rn(small_int_to_float(q1, 8.f), dd); }
+            else { v[2 * j] = fmaf(small_int_to_float(q0, 0.f), dd, mm); v[2 * j + 1] = fmaf(small_int_to_float(q1, 0.f), dd, mm); }
         }
     }
 }
@@ -293,7 +293,7 @@ __device__ __forceinline__ void q4_decode8(uint32_t dm, uint2 qs, int c, float (
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         const int q = (int)((w2[j >> 2] >> (8 * (j & 3))) & 0xF);
-        v[j] = (WT == BK_Q4_0) ? (float)(q - 8) * dd : (float)q * dd + mm;
+        v[j] = (WT == BK_Q4_0) ? __fmul_rn(small_int_to_float(q, 8.f), dd) : fmaf(small_int_to_float(q, 0.f), dd, mm);
     }
 }
 template <int WT, int NIT>
