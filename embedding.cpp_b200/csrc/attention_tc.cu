@@ -393,6 +393,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
 
 #include "attention_persist.cuh"
 #include "attention_loop.cuh"
+#include "attention_pack.cuh"
 #include "attention_stream.cuh"
 
 template <int DH, int G>
@@ -462,10 +463,21 @@ cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens
     return cudaErrorInvalidValue;
 }
 
-// box {dh, 64 rows} over qkv[rows][3d]; 128-byte swizzle for dh = 64, 64-byte for dh = 32
-bool make_tmap_attention(CUtensorMap *tm, const void *qkv, int d, int n_head, uint64_t rows) {
+cudaError_t launch_attention_packed(const CUtensorMap &tm64, const CUtensorMap &tm32, const CUtensorMap &tm16, const int32_t *cu_seqlens,
+                                    int n64, int n32, int n16, int d, int n_head, __half *out, int qmode, cudaStream_t st) {
+    if (n64 < 0 || n32 < 0 || n16 < 0 || d % n_head != 0) return cudaErrorInvalidValue;
+    if (n64 + n32 + n16 == 0) return cudaSuccess;
+    const PackCounts pc{n64, n32, n16};
     const int dh = d / n_head;
-    return make_tmap_f16_2d(tm, qkv, (uint64_t)3 * d, rows, (uint64_t)3 * d * 2, (uint32_t)dh, 64, dh == 64 ? 128 : 64);
+    if (dh == 64) return launch_att_pack<64>(tm64, tm32, tm16, cu_seqlens, pc, d, n_head, out, qmode, st);
+    if (dh == 32) return launch_att_pack<32>(tm64, tm32, tm16, cu_seqlens, pc, d, n_head, out, qmode, st);
+    return cudaErrorInvalidValue;
+}
+
+// box {dh, box_rows rows} over qkv[rows][3d]; 128-byte swizzle for dh = 64, 64-byte for dh = 32
+bool make_tmap_attention(CUtensorMap *tm, const void *qkv, int d, int n_head, uint64_t rows, int box_rows) {
+    const int dh = d / n_head;
+    return make_tmap_f16_2d(tm, qkv, (uint64_t)3 * d, rows, (uint64_t)3 * d * 2, (uint32_t)dh, (uint32_t)box_rows, dh == 64 ? 128 : 64);
 }
 
 }  // namespace bk

@@ -102,15 +102,14 @@ struct bk_engine {
     CUtensorMap to_qkv, to_pre, to_h;      // GEMM output maps (TMA stores), box {64, 128}
     CUtensorMap tr_x, tr_y;                // residual maps (unrounded x / y), box {64, 128}
     CUtensorMap to_xq, to_yq;              // Q4 models: the Q8-rounded copies as outputs of the fused GEMM + LayerNorm kernel
-    CUtensorMap ta_qkv;                    // attention's view of qkv: box {dh, 64 rows}
+    CUtensorMap ta_qkv, ta_qkv32, ta_qkv16;  // attention's views of qkv: boxes {dh, 64 | 32 | 16 rows} (the narrow ones: packed short sentences)
     // pinned staging
     // staged batch
     int st_T = 0, st_nseq = 0, st_maxlen = 0;  // last forward (hidden-state readback)
     // staged set (bench `value` leg): a whole job resident in HBM, cut into micro-batches of <= cap_tokens
-    // n_long / max_short: the slice has n_long sentences of more than 128 tokens (the on-device batcher puts them first) and the
-    // longest of the others has max_short tokens -> attention runs as two launches, each with the kernel made for its lengths;
-    // n_long = 0: one launch for all
-    struct Slice { int tok_off, seq_off, T, n_seq, max_len, n_long, max_short; };
+    // split: how many sentences of the slice fall into each length class of the attention kernels (the on-device batcher sorts by
+    // length, so the classes are consecutive runs of the packed batch) -> up to three attention launches per layer
+    struct Slice { int tok_off, seq_off, T, n_seq, max_len; AttSplit split; };
     std::vector<Slice> slices;
     int32_t *sg_tokens = nullptr, *sg_lens = nullptr;
     float *sg_out = nullptr;
@@ -121,8 +120,13 @@ struct bk_engine {
     __half *hidden = nullptr;  // [n_layer+1][cap_tokens][d]
     // CUDA graphs of the launch plan for small batches (latency path): key = (T, n_seq, max_len)
     struct GraphKey {
-        int T, n_seq, max_len, n_long, max_short, slot;
-        bool operator==(const GraphKey &o) const { return T == o.T && n_seq == o.n_seq && max_len == o.max_len && n_long == o.n_long && max_short == o.max_short && slot == o.slot; }
+        int T, n_seq, max_len, slot;
+        AttSplit split;
+        bool operator==(const GraphKey &o) const {
+            return T == o.T && n_seq == o.n_seq && max_len == o.max_len && slot == o.slot && split.n_long == o.split.n_long &&
+                   split.n_mid == o.split.n_mid && split.max_mid == o.split.max_mid && split.n64 == o.split.n64 && split.n32 == o.split.n32 &&
+                   split.n16 == o.split.n16;
+        }
     };
     struct GraphEntry { GraphKey key; cudaGraphExec_t exec; uint64_t last_use; };
     std::vector<GraphEntry> graphs;
@@ -426,7 +430,8 @@ BK_API int bk_engine_finalize(bk_engine *e) {
               make_tmap_f16_2d(&e->tr_y, e->y, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
               (!e->qmode || (make_tmap_f16_2d(&e->to_xq, e->xq, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M) &&
                              make_tmap_f16_2d(&e->to_yq, e->yq, d, T, d * 2, GEMM_OUT_BOX_N, GEMM_BLOCK_M))) &&
-              make_tmap_attention(&e->ta_qkv, e->qkv, (int)d, hp.n_head, T);
+              make_tmap_attention(&e->ta_qkv, e->qkv, (int)d, hp.n_head, T) && make_tmap_attention(&e->ta_qkv32, e->qkv, (int)d, hp.n_head, T, 32) &&
+              make_tmap_attention(&e->ta_qkv16, e->qkv, (int)d, hp.n_head, T, 16);
     if (!ok) return fail("cuTensorMapEncodeTiled failed for activation buffers");
     e->finalized = true;
     return 0;
@@ -473,7 +478,7 @@ int run_gemm(bk_engine *e, int kind, const CUtensorMap &tmA, const WeightMaps &W
 }
 
 // all kernels of one batch already resident on the device (tokens, lens in d_tokens/d_lens)
-int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens, int T, int n_seq, int max_len, int n_long, int max_short,
+int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens, int T, int n_seq, int max_len, const AttSplit &sp,
                    float *d_out) {
     const bk_hparams &hp = e->hp;
     const int d = hp.n_embd, f = hp.n_intermediate;
@@ -500,12 +505,20 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
         if (run_gemm(e, BK_K_GEMM_QKV, e->tm_x, L.tm_wqkv, L.pqkv, T, 3 * d, d, L.bqkv, nullptr, e->to_qkv, BK_EPI_BIAS)) return -1;
         {
             KTimer t(e, BK_K_ATTN);
-            if (n_long > 0 && n_long < n_seq) {  // long sentences: streaming kernel; the rest: one CTA per (sentence, head)
-                CK(launch_attention(e->ta_qkv, e->d_cu, n_long, max_len, d, hp.n_head, e->att, q, e->st));
-                CK(launch_attention(e->ta_qkv, e->d_cu + n_long, n_seq - n_long, max_short, d, hp.n_head, e->att, q, e->st));
-                e->launch_count += 2;
-            } else {
-                CK(launch_attention(e->ta_qkv, e->d_cu, n_seq, max_len, d, hp.n_head, e->att, q, e->st));
+            // sentences > 128 tokens: streaming kernel; 65..128 (and short ones when there are too few to pack): looping CTAs, one
+            // (sentence, head) per tile; <= 64 tokens: several sentences per tile (attention_pack.cuh)
+            const int n_short = sp.n64 + sp.n32 + sp.n16;
+            if (sp.n_long) {
+                CK(launch_attention(e->ta_qkv, e->d_cu, sp.n_long, max_len, d, hp.n_head, e->att, q, e->st));
+                e->launch_count++;
+            }
+            if (sp.n_mid) {
+                CK(launch_attention(e->ta_qkv, e->d_cu + sp.n_long, sp.n_mid, sp.max_mid, d, hp.n_head, e->att, q, e->st));
+                e->launch_count++;
+            }
+            if (n_short) {
+                CK(launch_attention_packed(e->ta_qkv, e->ta_qkv32, e->ta_qkv16, e->d_cu + sp.n_long + sp.n_mid, sp.n64, sp.n32, sp.n16, d, hp.n_head,
+                                           e->att, q, e->st));
                 e->launch_count++;
             }
         }
@@ -548,14 +561,15 @@ int forward_device(bk_engine *e, const int32_t *d_tokens, const int32_t *d_lens,
 // is seen and captured only when it comes back (capture + instantiation of 4 + 7L nodes costs several direct passes; traffic with
 // ever-new shapes must not pay it per call).  Direct small-batch launches use programmatic dependent launch like the captured plan.
 // Returns 1 = ran as a graph, 0 = caller must launch directly, < 0 error.
-int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, int n_long, int max_short) {
+int att_launches(const AttSplit &sp);
+int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, const AttSplit &sp) {
     e->graph_clock++;
-    const bk_engine::GraphKey key{T, n_seq, max_len, n_long, max_short, slot};
+    const bk_engine::GraphKey key{T, n_seq, max_len, slot, sp};
     for (auto &g : e->graphs)
         if (g.key == key) {
             g.last_use = e->graph_clock;
             CK(cudaGraphLaunch(g.exec, e->st));
-            e->launch_count += 4 + 7 * e->hp.n_layer;
+            e->launch_count += 4 + (6 + att_launches(sp)) * e->hp.n_layer;
             e->graph_hits++;
             return 1;
         }
@@ -570,7 +584,7 @@ int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, int n_l
     }
     cudaGraph_t graph = nullptr;
     CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
-    const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, max_len, n_long, max_short, e->d_out2[slot]);
+    const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, max_len, sp, e->d_out2[slot]);
     const cudaError_t ce = cudaStreamEndCapture(e->st, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     if (ce != cudaSuccess) return fail("cudaStreamEndCapture: %s", cudaGetErrorString(ce));
@@ -590,19 +604,33 @@ int forward_graph(bk_engine *e, int slot, int T, int n_seq, int max_len, int n_l
     return 1;
 }
 
-// the batcher sorts by length on the device, so the sentences of more than 128 tokens form a prefix of the packed batch whatever the
-// caller's order: their count and the longest of the rest (attention runs as two launches, each with the kernel made for its
-// lengths).  All long, or none: n_long = 0, one launch.
-void split_by_length(const int32_t *lens, int n_seq, int *n_long, int *max_short) {
-    int nl = 0, ms = 0;
+// The batcher sorts by length on the device, so the length classes of the attention kernels are consecutive runs of the packed
+// batch whatever the caller's order; the host only counts them (no sort): > 128 tokens | 65..128 | 33..64 | 17..32 | 1..16.
+// Fewer than kPackMin short sentences are not worth a launch of their own: they join the middle class (one per tile).
+// BERT_B200_ATT_PACK=0: never pack.
+constexpr int kPackMin = 8;
+void split_by_length(const int32_t *lens, int n_seq, AttSplit *sp) {
+    static const bool pack = [] { const char *v = getenv("BERT_B200_ATT_PACK"); return !v || atoi(v) != 0; }();
+    AttSplit a{0, 0, 0, 0, 0, 0};
+    int max_short = 0;
     for (int i = 0; i < n_seq; i++) {
-        if (lens[i] > 128) nl++;
-        else if (lens[i] > ms) ms = lens[i];
+        const int L = lens[i];
+        if (L > 128) a.n_long++;
+        else if (L > 64) { a.n_mid++; if (L > a.max_mid) a.max_mid = L; }
+        else {
+            if (L > 32) a.n64++; else if (L > 16) a.n32++; else a.n16++;
+            if (L > max_short) max_short = L;
+        }
     }
-    if (nl == n_seq) nl = 0;
-    *n_long = nl;
-    *max_short = nl ? ms : 0;
+    const int n_short = a.n64 + a.n32 + a.n16;
+    if (n_short && (!pack || n_short < kPackMin)) {
+        a.n_mid += n_short;
+        if (max_short > a.max_mid) a.max_mid = max_short;
+        a.n64 = a.n32 = a.n16 = 0;
+    }
+    *sp = a;
 }
+int att_launches(const AttSplit &sp) { return (sp.n_long ? 1 : 0) + (sp.n_mid ? 1 : 0) + ((sp.n64 + sp.n32 + sp.n16) ? 1 : 0); }
 
 int check_batch(bk_engine *e, const int32_t *lens, int n_seq, int *T_out, int *maxlen_out) {
     if (!e || !e->finalized) return fail("engine not finalized");
@@ -632,7 +660,7 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
     e->slices.clear();
     long long total = 0;
     for (int i = 0; i < n_seq;) {
-        bk_engine::Slice sl{(int)total, i, 0, 0, 0, 0, 0};
+        bk_engine::Slice sl{(int)total, i, 0, 0, 0, AttSplit{0, 0, 0, 0, 0, 0}};
         while (i < n_seq && sl.n_seq < e->cap_seqs) {
             if (lens[i] < 1 || lens[i] > e->hp.n_max_tokens) return fail("sentence %d has %d tokens (allowed 1..%d)", i, lens[i], e->hp.n_max_tokens);
             if (sl.T + lens[i] > e->cap_tokens) break;
@@ -641,7 +669,7 @@ BK_API int bk_engine_stage(bk_engine *e, const int32_t *tokens, const int32_t *l
             i++;
         }
         total += sl.T;
-        split_by_length(lens + sl.seq_off, sl.n_seq, &sl.n_long, &sl.max_short);
+        split_by_length(lens + sl.seq_off, sl.n_seq, &sl.split);
         e->slices.push_back(sl);
     }
     if ((size_t)total > e->sg_cap_tokens || (size_t)n_seq > e->sg_cap_seqs) {
@@ -672,8 +700,8 @@ static int enqueue_slot(bk_engine *e, int slot, int T, int n_seq, int mx, float 
     CK(cudaMemcpyAsync(e->d_tokens2[slot], e->h_tokens2[slot], (size_t)T * 4, cudaMemcpyHostToDevice, e->st));
     CK(cudaMemcpyAsync(e->d_lens2[slot], e->h_lens2[slot], (size_t)n_seq * 4, cudaMemcpyHostToDevice, e->st));
     e->st_T = T; e->st_nseq = n_seq; e->st_maxlen = mx;
-    int n_long = 0, max_short = 0;
-    split_by_length(lens, n_seq, &n_long, &max_short);
+    AttSplit sp;
+    split_by_length(lens, n_seq, &sp);
     const bool small = T <= e->graph_max_tokens && !e->keep_hidden && !e->timing;
     // the latency path: kernel boundaries are programmatic dependencies, so every kernel's set-up (and its launch) runs under the
     // tail of the one before it (common.cuh: pdl_wait) -- in the captured plan and in direct launches.  BERT_B200_PDL=0: plain edges.
@@ -681,13 +709,13 @@ static int enqueue_slot(bk_engine *e, int slot, int T, int n_seq, int mx, float 
     int ran = 0;
     if (small) {
         pdl_flag() = use_pdl;
-        ran = forward_graph(e, slot, T, n_seq, mx, n_long, max_short);
-        if (ran == 0) ran = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot]) ? -1 : 1;
+        ran = forward_graph(e, slot, T, n_seq, mx, sp);
+        if (ran == 0) ran = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, sp, e->d_out2[slot]) ? -1 : 1;
         pdl_flag() = false;
         if (ran < 0) return -1;
     } else {
         pdl_flag() = use_pdl && pdl_all();
-        const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, n_long, max_short, e->d_out2[slot]);
+        const int rc = forward_device(e, e->d_tokens2[slot], e->d_lens2[slot], T, n_seq, mx, sp, e->d_out2[slot]);
         pdl_flag() = false;
         if (rc) return -1;
     }
@@ -769,7 +797,7 @@ BK_API int bk_engine_run_staged(bk_engine *e, int32_t iters, int32_t time_kernel
     for (int i = 0; i < iters && rc == 0; i++)
         for (const auto &sl : e->slices) {
             e->st_T = sl.T; e->st_nseq = sl.n_seq; e->st_maxlen = sl.max_len;
-            rc = forward_device(e, e->sg_tokens + sl.tok_off, e->sg_lens + sl.seq_off, sl.T, sl.n_seq, sl.max_len, sl.n_long, sl.max_short,
+            rc = forward_device(e, e->sg_tokens + sl.tok_off, e->sg_lens + sl.seq_off, sl.T, sl.n_seq, sl.max_len, sl.split,
                                 e->sg_out + (size_t)sl.seq_off * e->hp.n_embd);
             if (rc) break;
         }

@@ -116,7 +116,15 @@ cudaError_t launch_pool_norm(const __half *x, const int32_t *cu_seqlens, const i
 // ---- attention_tc.cu ------------------------------------------------------------------------
 // qkv [T][3d] f16 (Q | K | V along the row) read through tmQKV (make_tmap_attention), out [T][d] f16;
 // one sentence = rows cu[s]..cu[s+1], at most 512 tokens; head size 32 or 64
-bool make_tmap_attention(CUtensorMap *tm, const void *qkv, int d, int n_head, uint64_t rows);
+bool make_tmap_attention(CUtensorMap *tm, const void *qkv, int d, int n_head, uint64_t rows, int box_rows = 64);
+// length classes of one packed, length-sorted batch (consecutive runs, longest first): n_long sentences of more than 128 tokens,
+// n_mid of up to max_mid <= 128 tokens that get a tile each, then n64 / n32 / n16 short ones (33..64 / 17..32 / 1..16 tokens) that
+// share tiles
+struct AttSplit { int n_long, n_mid, max_mid, n64, n32, n16; };
+// short sentences, several per 128-row tile (attention_pack.cuh): cu_seqlens points at the first of them; tm64 / tm32 / tm16 =
+// make_tmap_attention with boxes of 64 / 32 / 16 rows.  Bit-identical to launch_attention on the same sentences.
+cudaError_t launch_attention_packed(const CUtensorMap &tm64, const CUtensorMap &tm32, const CUtensorMap &tm16, const int32_t *cu_seqlens,
+                                    int n64, int n32, int n16, int d, int n_head, __half *out, int qmode, cudaStream_t st);
 cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens, int n_seq, int max_len, int d, int n_head,
                              __half *out, int qmode, cudaStream_t st);
 

@@ -206,6 +206,29 @@ BK_API int bk_test_attention(int device, int32_t n_seq, const int32_t *lens, int
     return 0;
 }
 
+BK_API int bk_test_attention_packed(int device, int32_t n64, int32_t n32, int32_t n16, const int32_t *lens, int32_t d, int32_t n_head,
+                                    const uint16_t *qkv, int32_t qmode, uint16_t *out) {
+    TCK(cudaSetDevice(device));
+    const int n_seq = n64 + n32 + n16;
+    for (int i = 0; i < n_seq; i++) {  // the classes must be consecutive runs: 33..64 | 17..32 | 1..16 tokens
+        const int lo = i < n64 ? 33 : i < n64 + n32 ? 17 : 1, hi = i < n64 ? 64 : i < n64 + n32 ? 32 : 16;
+        if (lens[i] < lo || lens[i] > hi) { fprintf(stderr, "bk_test_attention_packed: sentence %d has %d tokens, class %d..%d\n", i, lens[i], lo, hi); return -1; }
+    }
+    DevBuf dL, dC, dPos, dQ, dO;
+    int T, mx;
+    if (upload_lens(lens, n_seq, dL, dC, dPos, &T, &mx, 0)) return -1;
+    TCK(dQ.alloc(((size_t)T + 64) * 3 * d * 2)); TCK(dO.alloc((size_t)T * d * 2));   // the last slot's box may reach 63 rows past T
+    TCK(cudaMemset(dQ.p, 0, ((size_t)T + 64) * 3 * d * 2));
+    TCK(cudaMemcpy(dQ.p, qkv, (size_t)T * 3 * d * 2, cudaMemcpyHostToDevice));
+    CUtensorMap t64, t32, t16;
+    if (!make_tmap_attention(&t64, dQ.p, d, n_head, (uint64_t)T + 64, 64) || !make_tmap_attention(&t32, dQ.p, d, n_head, (uint64_t)T + 64, 32) ||
+        !make_tmap_attention(&t16, dQ.p, d, n_head, (uint64_t)T + 64, 16)) { fprintf(stderr, "bk_test_attention_packed: cuTensorMapEncodeTiled failed\n"); return -1; }
+    TCK(launch_attention_packed(t64, t32, t16, dC.as<int32_t>(), n64, n32, n16, d, n_head, dO.as<__half>(), qmode, 0));
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(out, dO.p, (size_t)T * d * 2, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t d, const uint16_t *x, float *out) {
     TCK(cudaSetDevice(device));
     DevBuf dL, dC, dPos, dX, dO;

@@ -132,6 +132,10 @@ BK_API int bk_test_add_ln(int device, int32_t T, int32_t d, float eps, const uin
 /* softmax(Q.K^T/sqrt(dh)).V per sentence and head on packed qkv[T][3d] (f16); bert.cpp:928-943 */
 BK_API int bk_test_attention(int device, int32_t n_seq, const int32_t *lens, int32_t d, int32_t n_head,
                              const uint16_t *qkv, int32_t qmode, uint16_t *out);
+/* the same for short sentences sharing 128-row tiles (attention_pack.cuh): lens = n64 sentences of 33..64 tokens, then n32 of 17..32,
+ * then n16 of 1..16 (the order the on-device batcher produces); qkv / out as above */
+BK_API int bk_test_attention_packed(int device, int32_t n64, int32_t n32, int32_t n16, const int32_t *lens, int32_t d, int32_t n_head,
+                                    const uint16_t *qkv, int32_t qmode, uint16_t *out);
 /* mean over tokens + L2 normalise; bert.cpp:995-1006 */
 BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t d, const uint16_t *x, float *out);
 /* the on-device batcher alone: lens[n_seq] and the ids concatenated in the caller's order -> order[n_seq] (sorted position ->

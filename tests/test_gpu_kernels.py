@@ -428,3 +428,26 @@ def test_attention_loop_kernel(lib, monkeypatch, d, H, n_seq, qmode):
         assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(out)) == 0
         outs.append(out)
     assert np.array_equal(outs[0].view(np.uint16), outs[1].view(np.uint16)), int((outs[0].view(np.uint16) != outs[1].view(np.uint16)).sum())
+
+
+@pytest.mark.parametrize("d,H,n64,n32,n16,qmode", [(768, 12, 37, 45, 203, 0), (768, 12, 1, 0, 0, 1), (128, 4, 0, 3, 1000, 0), (1024, 16, 64, 64, 64, 2),
+                                                   (256, 4, 2, 4, 8, 0), (384, 12, 0, 0, 17, 1), (768, 12, 300, 0, 0, 0)])
+def test_attention_packed_short_sentences(lib, monkeypatch, d, H, n64, n32, n16, qmode):
+    """attention_pack.cuh: 2 / 4 / 8 sentences of 33..64 / 17..32 / 1..16 tokens share one 128-row tile (slots on 16-key
+    boundaries, the other slots' P entries exact zeros).  Every class boundary, partly filled last tiles, more tiles than CTAs:
+    equal to the one-sentence-per-tile kernel bit for bit (a signed zero apart)."""
+    rng = np.random.default_rng(d + n64 + 3 * n32 + 7 * n16 + qmode)
+    lens = ([64, 33][:n64] + [int(v) for v in rng.integers(33, 65, max(0, n64 - 2))] + [32, 17][:n32] + [int(v) for v in rng.integers(17, 33, max(0, n32 - 2))] +
+            [16, 1][:n16] + [int(v) for v in rng.integers(1, 17, max(0, n16 - 2))])
+    assert len(lens) == n64 + n32 + n16
+    T = sum(lens)
+    qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
+    L = np.array(lens, np.int32)
+    packed = np.zeros((T, d), np.float16)
+    assert lib.bk_test_attention_packed(0, n64, n32, n16, L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(packed)) == 0
+    monkeypatch.setenv("BERT_B200_ATT_PERSIST", "0")
+    monkeypatch.setenv("BERT_B200_ATT_LOOP", "1")
+    alone = np.zeros((T, d), np.float16)
+    assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(alone)) == 0
+    assert np.isfinite(packed.astype(np.float32)).all()
+    assert np.array_equal(packed, alone), int((packed != alone).sum())     # float compare: -0 == +0
