@@ -408,7 +408,7 @@ def tokenizer_leg(lib, model, hp, n_texts, e2e_value):
             "tokenizer_texts_per_s_one_thread": per_thread, "tokenizer_threads_in_encode_batch": host_threads,
             "tokenizer_share_of_call_estimate": min(1.0, (n / (per_thread * host_threads)) / t_call),
             "unit_norm": bool(np.allclose(np.linalg.norm(out, axis=1), 1.0, atol=1e-3)),
-            "api": "bert_encode_batch (texts in, embeddings out; tokenisation spread over host threads, then one bert_eval_batch)"}
+            "api": "bert_encode_batch (texts in, embeddings out; chunks of 16384 texts, the next chunk tokenised on host threads while the current one is on the GPU)"}
 
 
 def run_workload(args, dist, gio, binding, lib, workload, full):

@@ -377,30 +377,50 @@ BERT_API void bert_tokenize(struct bert_ctx *ctx, const char *text, bert_vocab_i
 
 BERT_API void bert_encode_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n_batch_size, int32_t n_inputs, const char **texts,
                                 float **embeddings) {
-    (void)n_batch_size;  // the reference overrides it to 1 (bert.cpp:1128); here the whole call is one sorted batch
+    (void)n_batch_size;  // the reference overrides it to 1 (bert.cpp:1128); here the call is cut into micro-batches by token count
     if (!ctx || n_inputs <= 0) return;
     if (!ctx->tok_ok) { fprintf(stderr, "bert_encode_batch: this context was loaded without a usable tokenizer; outputs untouched\n"); return; }
     const int N = ctx->hp.n_max_tokens;
-    std::vector<int32_t> buf((size_t)n_inputs * N);
-    std::vector<int32_t *> ptrs(n_inputs);
-    std::vector<int32_t> lens(n_inputs);
-    // tokenisation is independent per text: spread it over host threads when the batch is large
-    const int hw = (int)std::max(1u, std::thread::hardware_concurrency());
-    const int nt = std::max(1, std::min({hw, n_inputs / 64, 32}));
-    auto tok_range = [&](int lo, int hi) {
-        for (int i = lo; i < hi; i++) {
-            ptrs[i] = buf.data() + (size_t)i * N;
-            bert_tokenize(ctx, texts[i], ptrs[i], &lens[i], N);
-        }
-    };
-    if (nt <= 1) tok_range(0, n_inputs);
-    else {
-        std::vector<std::thread> th;
-        const int per = (n_inputs + nt - 1) / nt;
-        for (int t = 0; t < nt; t++) th.emplace_back(tok_range, t * per, std::min(n_inputs, (t + 1) * per));
-        for (auto &t : th) t.join();
+    // Chunks of kChunk texts, two id buffers: chunk c + 1 is tokenised (spread over host threads) while chunk c is on the GPUs.
+    // (The reference tokenises and evaluates text by text, bert.cpp:1138-1190.)  A failing chunk leaves its own outputs untouched.
+    const int kChunk = 16384;
+    const int chunk_cap = std::min(n_inputs, kChunk);
+    struct Chunk {
+        std::unique_ptr<int32_t[]> ids;
+        std::vector<int32_t *> ptrs;
+        std::vector<int32_t> lens;
+    } ch[2];
+    for (auto &c : ch) {
+        c.ids.reset(new int32_t[(size_t)chunk_cap * N]);  // not zero-filled: only the tokens written are ever read
+        c.ptrs.resize(chunk_cap);
+        c.lens.resize(chunk_cap);
+        if (n_inputs <= kChunk) break;  // one chunk: one buffer
     }
-    bert_eval_batch(ctx, n_threads, n_inputs, ptrs.data(), lens.data(), embeddings);
+    const int hw = (int)std::max(1u, std::thread::hardware_concurrency());
+    auto tokenize = [&](Chunk &c, int first, int n) {
+        const int nt = std::max(1, std::min({hw, n / 64, 32}));  // tokenisation is independent per text
+        auto range = [&](int lo, int hi) {
+            for (int i = lo; i < hi; i++) {
+                c.ptrs[i] = c.ids.get() + (size_t)i * N;
+                bert_tokenize(ctx, texts[first + i], c.ptrs[i], &c.lens[i], N);
+            }
+        };
+        if (nt <= 1) { range(0, n); return; }
+        std::vector<std::thread> th;
+        const int per = (n + nt - 1) / nt;
+        for (int t = 0; t < nt; t++) th.emplace_back(range, std::min(n, t * per), std::min(n, (t + 1) * per));
+        for (auto &t : th) t.join();
+    };
+    tokenize(ch[0], 0, std::min(n_inputs, kChunk));
+    for (int first = 0, k = 0; first < n_inputs; first += kChunk, k++) {
+        const int n = std::min(kChunk, n_inputs - first);
+        Chunk &cur = ch[k & 1];
+        std::thread ahead;
+        if (first + kChunk < n_inputs)
+            ahead = std::thread([&, first, k] { tokenize(ch[(k + 1) & 1], first + kChunk, std::min(kChunk, n_inputs - first - kChunk)); });
+        bert_eval_batch(ctx, n_threads, n, cur.ptrs.data(), cur.lens.data(), embeddings + first);
+        if (ahead.joinable()) ahead.join();
+    }
 }
 
 BERT_API void bert_encode(struct bert_ctx *ctx, int32_t n_threads, const char *texts, float *embeddings) {
