@@ -65,7 +65,9 @@ BERT_API void bert_free(struct bert_ctx *ctx);
 BERT_API void bert_encode(struct bert_ctx *ctx, int32_t n_threads, const char *texts, float *embeddings);
 
 /* bert.h:54-60, bert.cpp:1119-1198: tokenise n_inputs texts, embed them all.  The reference
- * forces n_batch_size to 1 (bert.cpp:1128); here the whole call is one length-sorted batch. */
+ * forces n_batch_size to 1 (bert.cpp:1128); here it is ignored too: texts are tokenised on host threads in chunks of 16384
+ * (the next chunk while the current one is on the GPUs), each chunk is cut into token-budget micro-batches that the device sorts by
+ * length and packs. */
 BERT_API void bert_encode_batch(struct bert_ctx *ctx, int32_t n_threads, int32_t n_batch_size,
                                 int32_t n_inputs, const char **texts, float **embeddings);
 
