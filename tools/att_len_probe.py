@@ -19,12 +19,13 @@ if not os.path.exists(path):
 hp = gio.read_gguf(path).hparams()
 eng = binding.Engine(path, cap_tokens=65536, cap_seqs=8192)
 row = []
-for L in (16, 32, 48, 49, 64, 96, 128):
+LENS = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [16, 32, 48, 49, 64, 96, 128]
+for L in LENS:
     batch, _ = bench.make_batch(hp, 65536 // L if 65536 // L <= 8192 else 8192, L, seed=L)
     eng.stage(batch)
     eng.run_staged(2)
     eng.run_staged(4, time_kernels=True)
     ms, n = eng.kernel_ms()["attention"]
     row.append(f"L={L}: {1e3 * ms / n:.1f} us")
-print(f"{ftype} LOOP={os.environ.get('BERT_B200_ATT_LOOP', 'default')} PERSIST={os.environ.get('BERT_B200_ATT_PERSIST', 'default')}: " + "  ".join(row), flush=True)
+print(f"{ftype} LOOP={os.environ.get('BERT_B200_ATT_LOOP', 'default')} PERSIST={os.environ.get('BERT_B200_ATT_PERSIST', 'default')} STREAM={os.environ.get('BERT_B200_ATT_STREAM', 'default')} PACK={os.environ.get('BERT_B200_ATT_PACK', 'default')}: " + "  ".join(row), flush=True)
 eng.close()
