@@ -9,7 +9,7 @@ CXXFLAGS  := -O2 -std=c++17 -fPIC -fvisibility=hidden -Wall -Wextra -Wno-unused-
 SRC       := embedding.cpp_b200/csrc
 BUILD     ?= build
 OBJ       := $(BUILD)/obj
-CU_SRCS   := gemm_tcgen05.cu gemm_ws.cu gemm_ln.cu rowwise.cu attention_tc.cu engine.cu test_entry.cu
+CU_SRCS   := gemm_tcgen05.cu gemm_ws.cu gemm_ln.cu rowwise.cu attention_tc.cu engine.cu test_entry.cu batcher_static.cu
 CPP_SRCS  := api.cpp gguf.cpp tokenizer_wp.cpp quantize.cpp
 OBJS      := $(addprefix $(OBJ)/,$(CU_SRCS:.cu=.o) $(CPP_SRCS:.cpp=.o))
 

@@ -30,7 +30,7 @@ BK_SYMBOLS = ["bk_device_count", "bk_last_error", "bk_engine_create", "bk_engine
               "bk_engine_finalize", "bk_engine_forward", "bk_engine_submit", "bk_engine_collect", "bk_engine_submit_ragged", "bk_host_alloc", "bk_host_free",
               "bk_engine_graph_stats", "bk_bert_graph_stats", "bk_engine_stage", "bk_engine_run_staged", "bk_engine_read_output",
               "bk_engine_kernel_ms", "bk_engine_read_hidden", "bk_engine_set_keep_hidden", "bk_engine_launch_count", "bk_engine_check_guards", "bk_profiler_range",
-              "bk_test_gemm", "bk_test_gemm_ln", "bk_test_gelu", "bk_test_add_ln", "bk_test_attention", "bk_test_attention_packed", "bk_test_pool", "bk_test_batcher", "bk_test_embed_ln",
+              "bk_test_gemm", "bk_test_gemm_ln", "bk_test_gelu", "bk_test_add_ln", "bk_test_attention", "bk_test_attention_packed", "bk_test_pool", "bk_test_batcher", "bk_test_embed_ln", "bk_batcher_static_scratch",
               "bk_tokenizer_create", "bk_tokenizer_destroy", "bk_tokenizer_encode"]
 
 
@@ -116,6 +116,7 @@ def load_library(path: str | None = None):
     L.bk_test_pool.argtypes = [ctypes.c_int, i32, _i32p, i32, _u16p, _f32p]
     L.bk_test_batcher.argtypes = [ctypes.c_int, i32, _i32p, _i32p, _i32p, _i32p, _i32p, _i32p]
     L.bk_test_embed_ln.argtypes = [ctypes.c_int, i32, i32, i32, i32, i32, vp, vp, vp, _f32p, _f32p, ctypes.c_float, _i32p, _i32p, i32, _u16p, _u16p]
+    L.bk_batcher_static_scratch.argtypes = [ctypes.c_int, i32, i32, vp, vp, vp, vp, vp, vp, vp]  # device pointers + stream
     L.bk_tokenizer_create.restype = vp
     L.bk_tokenizer_create.argtypes = [ctypes.c_char_p, i64]
     L.bk_tokenizer_destroy.restype = None

@@ -142,6 +142,23 @@ BK_API int bk_test_pool(int device, int32_t n_seq, const int32_t *lens, int32_t 
  * caller index; stable, longest first), cu[n_seq+1], packed tok[T] and pos[T] */
 BK_API int bk_test_batcher(int device, int32_t n_seq, const int32_t *lens, const int32_t *tokens, int32_t *order, int32_t *cu,
                            int32_t *tok, int32_t *pos);
+/* The on-device batcher for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels and results as bk_test_batcher / the engine's batcher, but every pointer is a DEVICE pointer owned by the caller
+ * (d_lens[n_seq], d_tokens[n_tokens] in; d_order[n_seq], d_cu[n_seq+1], d_tok[n_tokens], d_pos[n_tokens] out), the two launches go
+ * to `stream` (a cudaStream_t; NULL = the default stream) without a synchronisation, and the kernels' scratch (two int32 per
+ * sentence) is a fixed 512 KiB __device__ array inside the library instead of a cudaMalloc'd workspace: the call allocates and
+ * frees nothing.  n_tokens = sum of the lengths (each clamped to 1..512 as everywhere else).
+ * Limit: n_seq <= BK_STATIC_BATCHER_MAX_SEQ, larger batches are rejected (BK_STATIC_E_TOO_LARGE, message on stderr).
+ * All calls on a device share the scratch: calls whose kernels overlap on the GPU (different streams) race; calls on one stream
+ * are safe.  The first call on each device resolves the array's address (cudaGetSymbolAddress) -- make it outside stream capture.
+ * Returns 0, or BK_STATIC_E_ARG / BK_STATIC_E_TOO_LARGE / BK_STATIC_E_CUDA. */
+#define BK_STATIC_BATCHER_MAX_SEQ 65536
+#define BK_STATIC_E_ARG (-1)
+#define BK_STATIC_E_TOO_LARGE (-2)
+#define BK_STATIC_E_CUDA (-3)
+BK_API int bk_batcher_static_scratch(int device, int32_t n_seq, int32_t n_tokens, const int32_t *d_lens, const int32_t *d_tokens,
+                                     int32_t *d_order, int32_t *d_cu, int32_t *d_tok, int32_t *d_pos, void *stream);
 /* embeddings gather + LayerNorm alone: x = LN((type[0] + word[tok]) + pos[p]) * gamma + beta, tables as raw GGUF bytes of `wtype`
  * (word [n_vocab][d], type [2][d], posw [n_pos][d]); x f16 [T][d], xq its Q8-rounded copy (qmode 1 / 2).  bert.cpp:868-898,
  * ggml_get_rows ggml.c:10108-10224 */
