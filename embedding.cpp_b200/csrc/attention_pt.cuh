@@ -1,0 +1,450 @@
+// attention_pt.cuh -- attention for launches with sentences of more than 128 tokens, P kept in tensor memory.
+// Included by attention_tc.cu (inside namespace bk, after attention_stream.cuh whose constants and structure it shares).
+//
+// attention_stream_kernel hands P to the tensor core through shared memory.  At L = 512 the shared-memory data pipe is then the
+// busiest unit of the SM (ncu, profiles/r02l_*: 49 % -- tensor-core operand reads 38 %, of which 22 points are the P.V and
+// row-sum MMAs re-reading P, plus 9 % for the P stores; MUFU 36 %, tensor pipe 29 %), and every softmax warp pays a
+// st.shared + fence.proxy.async round trip per chunk (12 % of its time).  Here a warp writes the f16 pairs of its 32 keys
+// back over the first 16 of the 32 score columns it has just read (tcgen05.st), and the P.V and row-sum MMAs take their A
+// operand from tensor memory (tcgen05.mma [d], [a], b-desc): P never touches shared memory.
+//
+// Consequences for the ring: a pass-B score slot now stays occupied until the MMAs that read its P have retired, so the slots
+// are dedicated instead of cycled -- two pass-B slots (chunk parity), handed back by the P.V warp's commit, and one pass-A slot,
+// handed back by the 16 softmax warps as soon as it is in registers.  Job order, arithmetic, rounding points and the order of
+// the 16-key MMA steps that accumulate O and the row sums are those of attention_stream_kernel: bit-identical results
+// (tests/test_gpu_kernels.py).  TMEM: pass-B slots [0, 128) [128, 256), pass-A slot [256, 384), O [384, 384 + dh), row sums
+// [384 + dh, +16).  A warp of key group g owns columns [32 g, 32 g + 32) of a slot on its 32 lanes: scores in, P (keys 32 g ..
+// 32 g + 15 in columns 32 g .. 32 g + 7, the next 16 keys in the next 8 columns) out; nobody else touches them in between.
+#pragma once
+
+// registers -> TMEM: lane i of the warp writes TMEM lane (taddr.lane + i), 16 consecutive columns
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+          "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+// D[tmem] (+)= A[tmem] . B[smem]: A is 128 lanes x 8 columns of f16 pairs (K = 16), K-major by construction
+__device__ __forceinline__ void umma_f16_ts_e(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(BK_ELECT_PROLOGUE ".reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// MN-major B operand of N = dh + 16 columns: the first atom (dh columns) is the V tile at `saddr`, the second atom lies `lbo_bytes`
+// further -- an all-ones tile, so that columns [dh, dh + 16) of the product are the row sums of A (canonical layout
+// ((8,n),(8,k)) : ((1,LBO),(8,SBO)), cute/atom/mma_traits_sm100.hpp; atoms along MN are LBO apart)
+template <int ROWB>
+__device__ __forceinline__ uint64_t umma_desc_mnmajor_ones(uint32_t saddr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((8 * ROWB) >> 4) << 32;       // SBO: next 8-key atom
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)(ROWB == 128 ? 2 : 4) << 61;
+    return d;
+}
+
+// A warp's 32 rows x 64 bytes (its 32 features of 32 query rows, one row per lane, pk = 16 f16 pairs) -> global memory through a
+// 2 KB staging tile, so that one store instruction covers 8 rows x 64 contiguous bytes (full 32-byte sectors) instead of 32 rows x
+// 16 bytes.  The direct form -- every lane storing its own row 16 bytes at a time -- made 1024 half-sector transactions per
+// query block and backed up the SM's load/store path, which the mbarrier operations of every other warp share: 13 % of the
+// kernel at L = 512 (tools/att_trace.py: all warps of the SM slow down for ~2000 cycles around each epilogue).
+// Chunk c of row R sits at 16-byte position (c + R / 2) % 4 of the row: conflict-free both ways.
+__device__ __forceinline__ void store_rows64(uint8_t *stage, const uint32_t (&pk)[16], __half *row0, size_t row_stride, int rows_valid, int lane) {
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+        *reinterpret_cast<uint4 *>(stage + lane * 64 + (((q + (lane >> 1)) & 3) << 4)) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int R = 8 * j + (lane >> 2), c = lane & 3;
+        const uint4 v = *reinterpret_cast<const uint4 *>(stage + R * 64 + (((c + (R >> 1)) & 3) << 4));
+        if (R < rows_valid) *reinterpret_cast<uint4 *>(row0 + (size_t)R * row_stride + c * 8) = v;
+    }
+    __syncwarp();
+}
+
+#ifdef BK_EXP_TRACE
+__device__ unsigned long long g_att_trace[8][1024];
+#define BK_TR(w, tag) do { if (trace_on && lane == 0) { g_att_trace[w][tr_n < 1023 ? tr_n++ : 1023] = ((unsigned long long)(tag) << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull); } } while (0)
+#else
+#define BK_TR(w, tag)
+#endif
+
+constexpr int kPtTail = 192 + 2 * 2048 + 8 * 2048;  // barriers + TMEM slot, two row-maximum exchange buffers, output staging
+
+template <int DH>
+__global__ void __launch_bounds__(kStreamThreads, 1)
+attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__restrict__ cu, int d, __half *__restrict__ out,
+                    int qmode, float scale) {
+    constexpr int ROWB = DH * 2;
+    constexpr int CW = 16;                 // score warp (TMA, S MMAs, TMEM allocation); CW + 1: P.V warp
+    constexpr uint32_t kASlot = 2 * kStreamKeys;           // TMEM column of the pass-A slot
+    constexpr uint32_t kOCol = 3 * kStreamKeys;            // O [384, 384+dh) | row sums [384+dh, +16)
+    extern __shared__ __align__(1024) uint8_t att_raw[];
+    uint8_t *smem = att_raw;
+
+    pdl_launch_dependents();
+    pdl_wait();  // the sequence bounds are read first thing
+    const int seq = blockIdx.z, head = blockIdx.y;
+    const int t0 = __ldg(cu + seq);
+    const int L = __ldg(cu + seq + 1) - t0;
+    if (L <= 0) return;
+    const int nqb = (L + kAttQ - 1) / kAttQ;
+    const int Lk16 = (L + 15) & ~15;
+    const int Lk64 = (L + 63) & ~63;
+    const int nc = (L + kStreamKeys - 1) / kStreamKeys;  // score chunks per pass
+
+    uint8_t *sQ = smem;                          // [2][128 rows]
+    uint8_t *sK = sQ + kStreamQ * kAttQ * ROWB;
+    uint8_t *sV = sK + Lk64 * ROWB;
+    uint8_t *sOnes = sV + Lk64 * ROWB;           // 16 keys x ROWB of f16 1.0: the second MN atom of every P.V step
+    uint8_t *tail = sOnes + 16 * ROWB;
+    uint64_t *bar_q = reinterpret_cast<uint64_t *>(tail);  // [2] Q buffer landed
+    uint64_t *bar_v = bar_q + 2;
+    uint64_t *bar_k = bar_q + 3;    // [4] keys [128 c, 128 c + 128) landed: the first score chunk does not wait for all of K
+    uint64_t *sfull = bar_q + 7;    // [3] score chunk complete in the slot (0, 1: pass B by chunk parity; 2: pass A)
+    uint64_t *sfree = bar_q + 10;   // [3] slot may be overwritten (0, 1: the MMAs that read its P have retired; 2: read by all 16 warps)
+    uint64_t *pfull = bar_q + 13;   // [2 slots][2 halves] P of a 64-key half written by the 8 warps of its two key groups
+    uint64_t *bar_o = bar_q + 17;   // O and row sums of a query block complete
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_q + 18);
+    // [2][4][128] partial row maxima, by block parity: a warp ahead of the others may publish the next block's maximum while a slow
+    // one still reads this block's (it cannot get further: pass-B job b + 2 is issued only when the P of job b, all 16 warps', was consumed)
+    float *red = reinterpret_cast<float *>(tail + 192);
+    uint8_t *stage = tail + 192 + 2 * 2048;                     // [8 warps][2 KB] output staging of the groups that store O
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef BK_EXP_TRACE
+    const bool trace_on = blockIdx.z == 64 && blockIdx.y == 0;
+    int tr_n = 0;
+    const int tw = warp >= CW ? 4 + (warp - CW) : warp == 0 ? 0 : warp == 5 ? 1 : warp == 10 ? 2 : warp == 15 ? 3 : 7;
+    BK_TR(tw, 0);
+#endif
+    if (warp == CW) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmQKV);
+            for (int i = 0; i < 4; i++) mbar_init(&bar_k[i], 1);
+            mbar_init(bar_v, 1); mbar_init(bar_o, 1);
+            mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
+            for (int i = 0; i < 3; i++) { mbar_init(&sfull[i], 1); mbar_init(&sfree[i], i < 2 ? 1 : 16); }
+            for (int i = 0; i < 4; i++) mbar_init(&pfull[i], 8);
+            mbar_fence_init();
+        }
+        __syncwarp();
+        {
+            // the loads first (they need the barriers only): their latency runs under the TMEM allocation and the CTA-wide sync
+            const int cq = head * DH, ck = d + head * DH, cv = 2 * d + head * DH;
+            const int n_box = Lk64 >> 6;
+            mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
+            tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, t0);
+            tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, t0 + 64);
+            for (int c = 0; c < nc; c++) {  // K in chunks of 128 keys (two 64-row boxes, the last chunk possibly one)
+                const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
+                mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
+                for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, t0 + (2 * c + b) * 64);
+            }
+            if (nqb > 1) {
+                uint8_t *q1 = sQ + kAttQ * ROWB;
+                mbar_expect_tx_e(&bar_q[1], (uint32_t)(kAttQ * ROWB));
+                tma_load_2d_e(q1, &tmQKV, &bar_q[1], cq, t0 + kAttQ);
+                tma_load_2d_e(q1 + 64 * ROWB, &tmQKV, &bar_q[1], cq, t0 + kAttQ + 64);
+            }
+            mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
+            for (int c = 0; c < n_box; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
+        }
+        for (int i = lane; i < 16 * ROWB / 4; i += 32) reinterpret_cast<uint32_t *>(sOnes)[i] = 0x3C003C00u;
+        fence_proxy_async_smem();
+        __syncwarp();
+        tmem_alloc<512>(tmem_slot);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    BK_TR(tw, 13);
+
+    if (warp == CW) {
+        // ================================================================ score warp: TMA loads, S = Q . K^T jobs
+        const int cq = head * DH;  // (Q(0), Q(1), K and V were requested in the prologue)
+        auto load_q = [&](int qb) {  // query block qb -> Q buffer qb % 2
+            uint8_t *q = sQ + (qb % kStreamQ) * kAttQ * ROWB;
+            uint64_t *bar = &bar_q[qb % kStreamQ];
+            mbar_expect_tx_e(bar, (uint32_t)(kAttQ * ROWB));
+            tma_load_2d_e(q, &tmQKV, bar, cq, t0 + qb * kAttQ);
+            tma_load_2d_e(q + 64 * ROWB, &tmQKV, bar, cq, t0 + qb * kAttQ + 64);
+        };
+
+        // score jobs in the order the softmax warps consume them: A(0,0..nc-1), then B(q,c) A(q+1,c) for c = 0..nc-1, q = 0..
+        const int n_jobs = 2 * nqb * nc;
+        uint32_t na = 0, nbj = 0;         // pass-A / pass-B jobs issued
+        bool prologue = true, job_a = true;
+        int jq = 0, jc = 0;               // B jobs: block jq, chunk jc; A jobs: block jq + 1 (block 0 in the prologue), chunk jc
+        const uint64_t dk0 = umma_desc_kmajor<ROWB>(smem_u32(sK));
+        const uint64_t dq0 = umma_desc_kmajor<ROWB>(smem_u32(sQ));
+        for (int js = 0; js < n_jobs; js++) {
+            BK_TR(tw, 20);
+            if (js < nc) mbar_wait(&bar_k[js], 0);  // prologue job A(0, js): the first user of key chunk js
+            uint32_t slot;
+            if (job_a) {
+                slot = 2;
+                if (na >= 1) mbar_wait(&sfree[2], (na - 1) & 1);  // the previous pass-A chunk is in the registers of all 16 warps
+                na++;
+            } else {
+                slot = nbj & 1;
+                if (nbj >= 2) mbar_wait(&sfree[slot], ((nbj >> 1) - 1) & 1);  // the MMAs that read the slot's P (two B jobs ago) have retired
+                nbj++;
+            }
+            const int blk = job_a ? (prologue ? 0 : jq + 1) : jq;
+            if (job_a && jc == 0) {
+                // first use of Q(blk).  Its buffer held Q(blk - 2), last read by the score MMAs of B(blk - 2, nc - 1) -- the pass-B
+                // job before the latest one, B(blk - 1, 0); no later job has been issued on its slot
+                if (blk >= 2) {
+                    const uint32_t lb = nbj - 2;
+                    mbar_wait(&sfull[lb & 1], (lb >> 1) & 1);
+#ifndef BK_EXP_NOQLOAD
+                    load_q(blk);
+#endif
+                }
+#ifdef BK_EXP_NOQLOAD
+                if (blk < 2)
+#endif
+                mbar_wait(&bar_q[blk % kStreamQ], (uint32_t)((blk / kStreamQ) & 1));
+            }
+            BK_TR(tw, 21);
+            const int n0 = jc * kStreamKeys;
+            const int nn = Lk16 - n0 < kStreamKeys ? Lk16 - n0 : kStreamKeys;
+            const uint64_t dq = dq0 + (uint64_t)(((blk % kStreamQ) * kAttQ * ROWB) >> 4);
+            const uint64_t dk = dk0 + (uint64_t)((n0 * ROWB) >> 4);
+            const uint32_t idesc = att_idesc((uint32_t)nn, 0);
+            tc_fence_after();
+#if defined(BK_EXP_NOSA)
+            if (slot != 2)
+#elif defined(BK_EXP_NOSB)
+            if (slot == 2)
+#endif
+#pragma unroll
+            for (int k = 0; k < DH / 16; k++)
+                umma_f16_e<1>(tmem_base + slot * kStreamKeys, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
+            umma_commit_e<1>(&sfull[slot]);
+            BK_TR(tw, 22);
+            if (prologue) {
+                if (++jc == nc) { prologue = false; job_a = false; jc = 0; }
+            } else if (!job_a) {
+                if (jq + 1 < nqb) job_a = true;
+                else if (++jc == nc) { jc = 0; jq++; }
+            } else {
+                job_a = false;
+                if (++jc == nc) { jc = 0; jq++; }
+            }
+        }
+    } else if (warp == CW + 1) {
+        // ================================================================ P.V warp: O += P . V, rowsum += P . 1, P read from the score slot
+        // one MMA per 16 keys: [O | row sums] += P . [V | 1], N = dh + 16 (the row sums come out of the same instruction)
+        const uint32_t idesc_pv = att_idesc(DH + kSumCols, 1);
+        const uint32_t v0 = smem_u32(sV), o1 = smem_u32(sOnes);
+        mbar_wait(bar_v, 0);
+        uint32_t pv_b = 0;  // pass-B jobs consumed
+        for (int qb = 0; qb < nqb; qb++) {
+            for (int c = 0; c < nc; c++, pv_b++) {
+                const uint32_t slot = pv_b & 1;
+                for (int sub = 0; sub < 2; sub++) {
+                    BK_TR(tw, 30 + sub);
+                    mbar_wait(&pfull[slot * 2 + sub], (pv_b >> 1) & 1);
+                    BK_TR(tw, 32 + sub);
+                    tc_fence_after();
+                    const int key0 = c * kStreamKeys + sub * 64;
+                    const int rem = Lk16 - key0;
+                    const int ksteps = rem >= 64 ? 4 : rem > 0 ? rem >> 4 : 0;
+                    const uint32_t pa = tmem_base + slot * kStreamKeys + (uint32_t)(sub * 64);  // keys 16 ks ..: group 2 sub + ks / 2, its columns 8 (ks % 2) ..
+#ifndef BK_EXP_NOPV
+                    for (int ks = 0; ks < ksteps; ks++) {
+                        const uint32_t va = v0 + (uint32_t)((key0 + 16 * ks) * ROWB);
+                        umma_f16_ts_e(tmem_base + kOCol, pa + (uint32_t)((ks >> 1) * 32 + (ks & 1) * 8), umma_desc_mnmajor_ones<ROWB>(va, o1 - va), idesc_pv,
+                                      (c | sub | ks) != 0);
+                    }
+#endif
+                }
+                umma_commit_e<1>(&sfree[slot]);
+                BK_TR(tw, 34);
+            }
+            umma_commit_e<1>(bar_o);
+        }
+    } else {
+        // ======================================================================= softmax warps
+        const int quad = warp & 3, g = warp >> 2;
+        const int r = quad * 32 + lane;                       // query row in the block == TMEM lane
+        const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
+        const uint32_t tcol = tlane + (uint32_t)(g * 32);     // my 32 columns of a slot
+        const int psub = g >> 1;                              // my 64-key half of a chunk
+        uint32_t na = 0;                                      // pass-A jobs done
+        uint32_t nb = 0;                                      // pass-B jobs done
+
+        // one pass-A job: fold this group's 32 keys of chunk c into the running row maximum
+        auto step_a = [&](int c, float mx) {
+            BK_TR(tw, 7);
+            mbar_wait(&sfull[2], na & 1);
+            BK_TR(tw, 8);
+            tc_fence_after();
+            const int key0 = c * kStreamKeys + g * 32;
+            if (key0 < L) {
+                uint32_t a[32];
+                tmem_ld_32x32(tcol + kASlot, a);
+                tmem_ld_wait();
+                const int nv = L - key0;
+                if (nv < 32) {  // keys past the sentence never enter
+#pragma unroll
+                    for (int i = 0; i < 32; i++) if (i >= nv) a[i] = 0xff800000u;
+                }
+                float m0 = mx, m1 = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    m0 = fmaxf(m0, fmaxf(__uint_as_float(a[i]), __uint_as_float(a[i + 1])));
+                    m1 = fmaxf(m1, fmaxf(__uint_as_float(a[i + 2]), __uint_as_float(a[i + 3])));
+                }
+                mx = fmaxf(m0, m1);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sfree[2]);
+            BK_TR(tw, 9);
+            na++;
+            return mx;
+        };
+        // O * (1 / sum p) of query block qb -> out rows
+        auto epilogue = [&](int qb) {
+            if (g >= DH / 32) return;  // groups 0 .. dh/32 - 1 each scale and store 32 features
+#ifdef BK_EXP_NOEPI
+            return;
+#endif
+            mbar_wait(bar_o, (uint32_t)(qb & 1));
+            tc_fence_after();
+            const float sum = __uint_as_float(tmem_ld_32x1(tlane + kOCol + (uint32_t)DH));
+            uint32_t a[32];
+            tmem_ld_32x32(tlane + kOCol + (uint32_t)(g * 32), a);
+            tmem_ld_wait();
+            const float inv = 1.0f / sum;
+            float o[32];
+#pragma unroll
+            for (int i = 0; i < 32; i++) o[i] = __uint_as_float(a[i]) * inv;
+            if (qmode) {  // the attention-output GEMM of a Q4 model quantises its input per 32 features (ggml.c:9493-9509)
+                float amax = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; i++) amax = fmaxf(amax, fabsf(o[i]));
+                float id, dq;
+                q8_scales(amax, qmode, id, dq);
+#pragma unroll
+                for (int i = 0; i < 32; i++) o[i] = q8_round(o[i], id, dq);
+            }
+            const int q0 = qb * kAttQ;
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) pk[i] = pack_h2(o[2 * i], o[2 * i + 1]);
+            store_rows64(stage + warp * 2048, pk, out + (size_t)(t0 + q0 + quad * 32) * d + (size_t)head * DH + g * 32, (size_t)d, L - q0 - quad * 32, lane);
+        };
+
+        float mx_next = -INFINITY;
+        for (int c = 0; c < nc; c++) mx_next = step_a(c, mx_next);  // pass A of block 0 (not overlapped)
+        for (int qb = 0; qb < nqb; qb++) {
+            // ---- row maximum of this block over the four groups
+            float mx = mx_next;
+            {
+                float *rb = red + (qb & 1) * 512;
+                rb[g * 128 + r] = mx;
+                BK_TR(tw, 10);
+                named_bar_sync(1, 512);
+                BK_TR(tw, 11);
+#pragma unroll
+                for (int gg = 0; gg < 4; gg++) mx = fmaxf(mx, rb[gg * 128 + r]);
+            }
+            mx *= scale;  // max(s*scale) == max(s)*scale for scale > 0 (rounding is monotonic)
+            mx_next = -INFINITY;
+            // the previous block's O: read before this block's first P is handed over (the MMA on it overwrites O); the groups
+            // that read O (0 .. dh/32 - 1) belong to the first 64-key half, whose P the first MMA of the block waits for
+            if (qb > 0) epilogue(qb - 1);
+            BK_TR(tw, 12);
+            for (int c = 0; c < nc; c++) {
+                // ---- pass B job: p = f16(exp(f16(s*scale - max))) for my 32 keys of chunk c, written back over the scores
+                const uint32_t slot = nb & 1;
+                BK_TR(tw, 1);
+                mbar_wait(&sfull[slot], (nb >> 1) & 1);
+                BK_TR(tw, 2);
+                tc_fence_after();
+                const int key0 = c * kStreamKeys + g * 32;
+                if (key0 < L) {  // otherwise no real key: the MMA does not read these P columns
+                    uint32_t a[32];
+                    tmem_ld_32x32(tcol + slot * kStreamKeys, a);
+                    tmem_ld_wait();
+                    BK_TR(tw, 3);
+                    const int nv = L - key0;
+                    if (nv < 32) {  // s = -inf -> p = 0 exactly
+#pragma unroll
+                        for (int i = 0; i < 32; i++) if (i >= nv) a[i] = 0xff800000u;
+                    }
+                    uint32_t pk[16];
+                    const float2 sc2 = make_float2(scale, scale), nmx2 = make_float2(-mx, -mx), l2e = make_float2(1.4426950408889634f, 1.4426950408889634f);
+#pragma unroll
+                    for (int i = 0; i < 32; i += 2) {  // same instruction sequence as attention_tc_kernel
+                        float2 x;
+                        if (DH == 64)
+                            x = __ffma2_rn(make_float2(__uint_as_float(a[i]), __uint_as_float(a[i + 1])), sc2, nmx2);
+                        else
+                            x = __fadd2_rn(make_float2(__fmul_rn(__uint_as_float(a[i]), scale), __fmul_rn(__uint_as_float(a[i + 1]), scale)), nmx2);
+                        const float2 z = __fmul2_rn(__half22float2(__floats2half2_rn(x.x, x.y)), l2e);
+                        float2 e;
+#ifdef BK_EXP_NOEXP
+                        e = z;
+#else
+                        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(z.x));
+                        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(z.y));
+#endif
+                        const __half2 hp = __floats2half2_rn(e.x, e.y);
+                        pk[i >> 1] = *reinterpret_cast<const uint32_t *>(&hp);
+                    }
+                    BK_TR(tw, 4);
+                    tmem_st_32x16(tcol + slot * kStreamKeys, pk);
+                    tmem_st_wait();
+                    BK_TR(tw, 5);
+                }
+                tc_fence_before();  // P in tensor memory -> visible to the MMAs issued behind the barrier
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&pfull[slot * 2 + psub]);
+                BK_TR(tw, 6);
+                nb++;
+                // ---- pass A job of the next block, same chunk
+                if (qb + 1 < nqb) mx_next = step_a(c, mx_next);
+            }
+        }
+        epilogue(nqb - 1);
+    }
+    BK_TR(tw, 14);
+
+    tc_fence_before();
+    __syncthreads();
+    BK_TR(tw, 15);
+    if (warp == CW) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+template <int DH>
+static cudaError_t launch_att_pt(const CUtensorMap &tm, const int32_t *cu, int n_seq, int max_len, int d, int n_head, __half *out,
+                                 int qmode, cudaStream_t st) {
+    const int Lk64 = (max_len + 63) & ~63;
+    const size_t smem = (size_t)kStreamQ * kAttQ * DH * 2 + (size_t)2 * Lk64 * DH * 2 + 16 * DH * 2 + kPtTail;
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        cudaError_t err = cudaFuncSetAttribute(attention_pt_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (err != cudaSuccess) return err;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    dim3 grid(1, n_head, n_seq);
+    const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934
+    LaunchConfig lc(grid, dim3(kStreamThreads), smem, st);
+    return cudaLaunchKernelEx(&lc.cfg, attention_pt_kernel<DH>, tm, cu, d, out, qmode, scale);
+}

@@ -31,6 +31,8 @@
 namespace bk {
 
 constexpr int kAttQ = 128;  // queries per CTA
+constexpr bool kAttPtDefault = true;     // attention_pt.cuh for launches with sentences > 128 tokens (A/B: BERT_B200_ATT_PT)
+constexpr bool kAttDuoDefault = false;   // attention_duo.cuh for launches with sentences > 128 tokens (A/B: BERT_B200_ATT_DUO)
 constexpr bool kAttLoopDefault = true;   // attention_loop.cuh for launches of sentences <= 128 tokens (A/B: BERT_B200_ATT_LOOP)
 
 // K-major operand tile whose rows are ROWB = 64 or 128 bytes (dh = 32 / 64 halves): TMA SWIZZLE_64B / 128B
@@ -395,6 +397,8 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
 #include "attention_loop.cuh"
 #include "attention_pack.cuh"
 #include "attention_stream.cuh"
+#include "attention_duo.cuh"
+#include "attention_pt.cuh"
 
 template <int DH, int G>
 static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_seq, int max_len, int d, int n_head, __half *out,
@@ -447,6 +451,18 @@ cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens
     // launches with sentences of more than 128 tokens: scores streamed through a TMEM ring (BERT_B200_ATT_STREAM=0: whole
     // score block resident, attention_tc_kernel)
     const char *sv = getenv("BERT_B200_ATT_STREAM");
+    // P kept in tensor memory (attention_pt.cuh); BERT_B200_ATT_PT=0: through shared memory (attention_stream.cuh)
+    const char *tv = getenv("BERT_B200_ATT_PT");
+    if (max_len > kAttQ && (!sv || atoi(sv) != 0) && env_g == 0 && (tv ? atoi(tv) != 0 : kAttPtDefault)) {
+        if (dh == 64) return launch_att_pt<64>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
+        if (dh == 32) return launch_att_pt<32>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
+    }
+    // two query blocks in flight per CTA (attention_duo.cuh, BERT_B200_ATT_DUO=1; measured no faster than one block at a time)
+    const char *dv = getenv("BERT_B200_ATT_DUO");
+    if (max_len > kAttQ && (!sv || atoi(sv) != 0) && env_g == 0 && (dv ? atoi(dv) != 0 : kAttDuoDefault)) {
+        if (dh == 64) return launch_att_duo<64>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
+        if (dh == 32) return launch_att_duo<32>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
+    }
     if (max_len > kAttQ && (!sv || atoi(sv) != 0) && env_g == 0) {
         if (dh == 64) return launch_att_stream<64>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
         if (dh == 32) return launch_att_stream<32>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
@@ -481,3 +497,9 @@ bool make_tmap_attention(CUtensorMap *tm, const void *qkv, int d, int n_head, ui
 }
 
 }  // namespace bk
+
+#ifdef BK_EXP_TRACE
+extern "C" __attribute__((visibility("default"))) int bk_debug_att_trace(unsigned long long *out) {
+    return (int)cudaMemcpyFromSymbol(out, bk::g_att_trace, sizeof(unsigned long long) * 8 * 1024);
+}
+#endif
