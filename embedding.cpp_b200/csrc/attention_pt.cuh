@@ -74,15 +74,15 @@ __device__ unsigned long long g_att_trace[8][1024];
 #define BK_TR(w, tag)
 #endif
 
-constexpr int kPtTail = 192 + 2 * 2048 + 8 * 2048;  // barriers + TMEM slot, two row-maximum exchange buffers, output staging
+constexpr int kPtThreads = kStreamThreads + 128;  // 16 softmax warps, score warp, P.V warp, 4 output warps
+constexpr int kPtTail = 192 + 2 * 2048 + 4 * 2048;  // barriers + TMEM slot, two row-maximum exchange buffers, output staging
 
 template <int DH>
-__global__ void __launch_bounds__(kStreamThreads, 1)
+__global__ void __launch_bounds__(kPtThreads, 1)
 attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__restrict__ cu, int d, __half *__restrict__ out,
                     int qmode, float scale) {
     constexpr int ROWB = DH * 2;
     constexpr int CW = 16;                 // score warp (TMA, S MMAs, TMEM allocation); CW + 1: P.V warp
-    constexpr uint32_t kASlot = 2 * kStreamKeys;           // TMEM column of the pass-A slot
     constexpr uint32_t kOCol = 3 * kStreamKeys;            // O [384, 384+dh) | row sums [384+dh, +16)
     extern __shared__ __align__(1024) uint8_t att_raw[];
     uint8_t *smem = att_raw;
@@ -110,24 +110,25 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
     uint64_t *sfree = bar_q + 10;   // [3] slot may be overwritten (0, 1: the MMAs that read its P have retired; 2: read by all 16 warps)
     uint64_t *pfull = bar_q + 13;   // [2 slots][2 halves] P of a 64-key half written by the 8 warps of its two key groups
     uint64_t *bar_o = bar_q + 17;   // O and row sums of a query block complete
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_q + 18);
+    uint64_t *ofree = bar_q + 18;   // O and the row sums are in the registers of the 4 output warps
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_q + 19);
     // [2][4][128] partial row maxima, by block parity: a warp ahead of the others may publish the next block's maximum while a slow
     // one still reads this block's (it cannot get further: pass-B job b + 2 is issued only when the P of job b, all 16 warps', was consumed)
     float *red = reinterpret_cast<float *>(tail + 192);
-    uint8_t *stage = tail + 192 + 2 * 2048;                     // [8 warps][2 KB] output staging of the groups that store O
+    uint8_t *stage = tail + 192 + 2 * 2048;                     // [4 warps][2 KB] output staging
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #ifdef BK_EXP_TRACE
     const bool trace_on = blockIdx.z == 64 && blockIdx.y == 0;
     int tr_n = 0;
-    const int tw = warp >= CW ? 4 + (warp - CW) : warp == 0 ? 0 : warp == 5 ? 1 : warp == 10 ? 2 : warp == 15 ? 3 : 7;
+    const int tw = warp == 20 ? 6 : warp >= CW + 2 ? 7 : warp >= CW ? 4 + (warp - CW) : warp == 0 ? 0 : warp == 5 ? 1 : warp == 10 ? 2 : warp == 15 ? 3 : 7;
     BK_TR(tw, 0);
 #endif
     if (warp == CW) {
         if (lane == 0) {
             tma_prefetch_desc(&tmQKV);
             for (int i = 0; i < 4; i++) mbar_init(&bar_k[i], 1);
-            mbar_init(bar_v, 1); mbar_init(bar_o, 1);
+            mbar_init(bar_v, 1); mbar_init(bar_o, 1); mbar_init(ofree, 4);
             mbar_init(&bar_q[0], 1); mbar_init(&bar_q[1], 1);
             for (int i = 0; i < 3; i++) { mbar_init(&sfull[i], 1); mbar_init(&sfree[i], i < 2 ? 1 : 16); }
             for (int i = 0; i < 4; i++) mbar_init(&pfull[i], 8);
@@ -155,6 +156,7 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
             mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
             for (int c = 0; c < n_box; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
         }
+    } else if (warp == CW + 1) {  // meanwhile: the all-ones tile and the TMEM allocation
         for (int i = lane; i < 16 * ROWB / 4; i += 32) reinterpret_cast<uint32_t *>(sOnes)[i] = 0x3C003C00u;
         fence_proxy_async_smem();
         __syncwarp();
@@ -178,8 +180,11 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         };
 
         // score jobs in the order the softmax warps consume them: A(0,0..nc-1), then B(q,c) A(q+1,c) for c = 0..nc-1, q = 0..
+        // Slots: pass B of chunk number b -> slot b % 2, pass A -> slot 2; the prologue A(0,c), which has the ring to itself, cycles
+        // through all three (c -> (c + 2) % 3) so that its MMAs do not wait for the round trip of one slot.
         const int n_jobs = 2 * nqb * nc;
-        uint32_t na = 0, nbj = 0;         // pass-A / pass-B jobs issued
+        uint32_t used = 0, par = 0;       // per slot (bit): has been used / number of uses so far is odd
+        uint32_t nbj = 0;                 // pass-B jobs issued
         bool prologue = true, job_a = true;
         int jq = 0, jc = 0;               // B jobs: block jq, chunk jc; A jobs: block jq + 1 (block 0 in the prologue), chunk jc
         const uint64_t dk0 = umma_desc_kmajor<ROWB>(smem_u32(sK));
@@ -187,32 +192,15 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         for (int js = 0; js < n_jobs; js++) {
             BK_TR(tw, 20);
             if (js < nc) mbar_wait(&bar_k[js], 0);  // prologue job A(0, js): the first user of key chunk js
-            uint32_t slot;
-            if (job_a) {
-                slot = 2;
-                if (na >= 1) mbar_wait(&sfree[2], (na - 1) & 1);  // the previous pass-A chunk is in the registers of all 16 warps
-                na++;
-            } else {
-                slot = nbj & 1;
-                if (nbj >= 2) mbar_wait(&sfree[slot], ((nbj >> 1) - 1) & 1);  // the MMAs that read the slot's P (two B jobs ago) have retired
-                nbj++;
-            }
+            const uint32_t slot = prologue ? (uint32_t)((js + 2) % 3) : job_a ? 2u : (nbj & 1);
+            // the previous contents have been consumed: slot 2 and the prologue's slots -- in the registers of all 16 warps; a pass-B
+            // slot -- the MMAs that read its P have retired
+            if ((used >> slot) & 1) mbar_wait(&sfree[slot], ((par >> slot) & 1) ^ 1);
+            used |= 1u << slot;
+            par ^= 1u << slot;
+            if (!job_a) nbj++;
             const int blk = job_a ? (prologue ? 0 : jq + 1) : jq;
-            if (job_a && jc == 0) {
-                // first use of Q(blk).  Its buffer held Q(blk - 2), last read by the score MMAs of B(blk - 2, nc - 1) -- the pass-B
-                // job before the latest one, B(blk - 1, 0); no later job has been issued on its slot
-                if (blk >= 2) {
-                    const uint32_t lb = nbj - 2;
-                    mbar_wait(&sfull[lb & 1], (lb >> 1) & 1);
-#ifndef BK_EXP_NOQLOAD
-                    load_q(blk);
-#endif
-                }
-#ifdef BK_EXP_NOQLOAD
-                if (blk < 2)
-#endif
-                mbar_wait(&bar_q[blk % kStreamQ], (uint32_t)((blk / kStreamQ) & 1));
-            }
+            if (job_a && jc == 0) mbar_wait(&bar_q[blk % kStreamQ], (uint32_t)((blk / kStreamQ) & 1));  // first use of Q(blk)
             BK_TR(tw, 21);
             const int n0 = jc * kStreamKeys;
             const int nn = Lk16 - n0 < kStreamKeys ? Lk16 - n0 : kStreamKeys;
@@ -220,11 +208,6 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
             const uint64_t dk = dk0 + (uint64_t)((n0 * ROWB) >> 4);
             const uint32_t idesc = att_idesc((uint32_t)nn, 0);
             tc_fence_after();
-#if defined(BK_EXP_NOSA)
-            if (slot != 2)
-#elif defined(BK_EXP_NOSB)
-            if (slot == 2)
-#endif
 #pragma unroll
             for (int k = 0; k < DH / 16; k++)
                 umma_f16_e<1>(tmem_base + slot * kStreamKeys, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
@@ -237,7 +220,16 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                 else if (++jc == nc) { jc = 0; jq++; }
             } else {
                 job_a = false;
-                if (++jc == nc) { jc = 0; jq++; }
+                if (++jc == nc) {
+                    // A(jq + 1, nc - 1) was the last job of this round; the one before it, B(jq, nc - 1), the last reader of Q(jq).
+                    // Refill that buffer with Q(jq + 2) now, a whole round of pass-B jobs before its first use.
+                    if (jq + 2 < nqb) {
+                        const uint32_t lbs = (nbj - 1) & 1;  // slot of B(jq, nc - 1): its latest use
+                        mbar_wait(&sfull[lbs], ((par >> lbs) & 1) ^ 1);
+                        load_q(jq + 2);
+                    }
+                    jc = 0; jq++;
+                }
             }
         }
     } else if (warp == CW + 1) {
@@ -245,6 +237,16 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         // one MMA per 16 keys: [O | row sums] += P . [V | 1], N = dh + 16 (the row sums come out of the same instruction)
         const uint32_t idesc_pv = att_idesc(DH + kSumCols, 1);
         const uint32_t v0 = smem_u32(sV), o1 = smem_u32(sOnes);
+        uint32_t ppar = 0;  // per pass-B slot (bit): number of hand-overs so far is odd
+        // the prologue's chunks 1 and 2 went through the pass-B slots 0 and 1: the 16 warps report "read" on the P barriers, and the
+        // slot is handed back the way it always is -- by a commit from this warp (nothing outstanding: it arrives at once)
+        for (int c = 1; c < nc && c < 3; c++) {
+            const uint32_t slot = (uint32_t)(c - 1);
+            mbar_wait(&pfull[slot * 2], 0);
+            mbar_wait(&pfull[slot * 2 + 1], 0);
+            umma_commit_e<1>(&sfree[slot]);
+            ppar ^= 1u << slot;
+        }
         mbar_wait(bar_v, 0);
         uint32_t pv_b = 0;  // pass-B jobs consumed
         for (int qb = 0; qb < nqb; qb++) {
@@ -252,25 +254,70 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                 const uint32_t slot = pv_b & 1;
                 for (int sub = 0; sub < 2; sub++) {
                     BK_TR(tw, 30 + sub);
-                    mbar_wait(&pfull[slot * 2 + sub], (pv_b >> 1) & 1);
+                    mbar_wait(&pfull[slot * 2 + sub], (ppar >> slot) & 1);
+                    if (qb > 0 && (c | sub) == 0) mbar_wait(ofree, (uint32_t)((qb - 1) & 1));  // the first MMA of a block overwrites O
                     BK_TR(tw, 32 + sub);
                     tc_fence_after();
                     const int key0 = c * kStreamKeys + sub * 64;
                     const int rem = Lk16 - key0;
                     const int ksteps = rem >= 64 ? 4 : rem > 0 ? rem >> 4 : 0;
                     const uint32_t pa = tmem_base + slot * kStreamKeys + (uint32_t)(sub * 64);  // keys 16 ks ..: group 2 sub + ks / 2, its columns 8 (ks % 2) ..
-#ifndef BK_EXP_NOPV
                     for (int ks = 0; ks < ksteps; ks++) {
                         const uint32_t va = v0 + (uint32_t)((key0 + 16 * ks) * ROWB);
                         umma_f16_ts_e(tmem_base + kOCol, pa + (uint32_t)((ks >> 1) * 32 + (ks & 1) * 8), umma_desc_mnmajor_ones<ROWB>(va, o1 - va), idesc_pv,
                                       (c | sub | ks) != 0);
                     }
-#endif
                 }
                 umma_commit_e<1>(&sfree[slot]);
+                ppar ^= 1u << slot;
                 BK_TR(tw, 34);
             }
             umma_commit_e<1>(bar_o);
+        }
+    } else if (warp >= CW + 2) {
+        // ======================================================================= output warps: O * (1 / sum p) -> out rows
+        // One warp per TMEM lane quarter.  The softmax warps never touch O: while they are in the next block's first chunk, these
+        // warps take the finished block out of tensor memory (the P.V warp's first MMA of that block waits for `ofree`), scale,
+        // quantise for Q4 models and store.
+        const int quad = warp & 3;
+        const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
+        uint8_t *st = stage + (warp - (CW + 2)) * 2048;
+        for (int qb = 0; qb < nqb; qb++) {
+            mbar_wait(bar_o, (uint32_t)(qb & 1));
+            BK_TR(tw, 16);
+            tc_fence_after();
+            const float sum = __uint_as_float(tmem_ld_32x1(tlane + kOCol + (uint32_t)DH));
+            const float inv = 1.0f / sum;
+            const int row0 = qb * kAttQ + quad * 32;
+#pragma unroll
+            for (int hf = 0; hf < DH / 32; hf++) {
+                uint32_t a[32];
+                tmem_ld_32x32(tlane + kOCol + (uint32_t)(hf * 32), a);
+                tmem_ld_wait();
+                if (hf == DH / 32 - 1) {  // all of O is in registers (the P.V warp is at least a chunk of exponentials away from needing it)
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(ofree);
+                    BK_TR(tw, 17);
+                }
+                float o[32];
+#pragma unroll
+                for (int i = 0; i < 32; i++) o[i] = __uint_as_float(a[i]) * inv;
+                if (qmode) {  // the attention-output GEMM of a Q4 model quantises its input per 32 features (ggml.c:9493-9509)
+                    float amax = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 32; i++) amax = fmaxf(amax, fabsf(o[i]));
+                    float id, dq;
+                    q8_scales(amax, qmode, id, dq);
+#pragma unroll
+                    for (int i = 0; i < 32; i++) o[i] = q8_round(o[i], id, dq);
+                }
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 16; i++) pk[i] = pack_h2(o[2 * i], o[2 * i + 1]);
+                store_rows64(st, pk, out + (size_t)(t0 + row0) * d + (size_t)head * DH + hf * 32, (size_t)d, L - row0, lane);
+            }
+            BK_TR(tw, 18);
         }
     } else {
         // ======================================================================= softmax warps
@@ -279,19 +326,20 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
         const uint32_t tcol = tlane + (uint32_t)(g * 32);     // my 32 columns of a slot
         const int psub = g >> 1;                              // my 64-key half of a chunk
-        uint32_t na = 0;                                      // pass-A jobs done
+        uint32_t spar = 0;                                    // per score slot (bit): number of chunks consumed from it so far is odd
         uint32_t nb = 0;                                      // pass-B jobs done
 
         // one pass-A job: fold this group's 32 keys of chunk c into the running row maximum
-        auto step_a = [&](int c, float mx) {
+        auto step_a = [&](int c, float mx, uint32_t slot) {
             BK_TR(tw, 7);
-            mbar_wait(&sfull[2], na & 1);
+            mbar_wait(&sfull[slot], (spar >> slot) & 1);
+            spar ^= 1u << slot;
             BK_TR(tw, 8);
             tc_fence_after();
             const int key0 = c * kStreamKeys + g * 32;
             if (key0 < L) {
                 uint32_t a[32];
-                tmem_ld_32x32(tcol + kASlot, a);
+                tmem_ld_32x32(tcol + slot * kStreamKeys, a);
                 tmem_ld_wait();
                 const int nv = L - key0;
                 if (nv < 32) {  // keys past the sentence never enter
@@ -308,45 +356,12 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sfree[2]);
+            if (lane == 0) mbar_arrive(slot == 2 ? &sfree[2] : &pfull[slot * 2 + psub]);  // (a prologue chunk in a pass-B slot: see the P.V warp)
             BK_TR(tw, 9);
-            na++;
             return mx;
         };
-        // O * (1 / sum p) of query block qb -> out rows
-        auto epilogue = [&](int qb) {
-            if (g >= DH / 32) return;  // groups 0 .. dh/32 - 1 each scale and store 32 features
-#ifdef BK_EXP_NOEPI
-            return;
-#endif
-            mbar_wait(bar_o, (uint32_t)(qb & 1));
-            tc_fence_after();
-            const float sum = __uint_as_float(tmem_ld_32x1(tlane + kOCol + (uint32_t)DH));
-            uint32_t a[32];
-            tmem_ld_32x32(tlane + kOCol + (uint32_t)(g * 32), a);
-            tmem_ld_wait();
-            const float inv = 1.0f / sum;
-            float o[32];
-#pragma unroll
-            for (int i = 0; i < 32; i++) o[i] = __uint_as_float(a[i]) * inv;
-            if (qmode) {  // the attention-output GEMM of a Q4 model quantises its input per 32 features (ggml.c:9493-9509)
-                float amax = 0.f;
-#pragma unroll
-                for (int i = 0; i < 32; i++) amax = fmaxf(amax, fabsf(o[i]));
-                float id, dq;
-                q8_scales(amax, qmode, id, dq);
-#pragma unroll
-                for (int i = 0; i < 32; i++) o[i] = q8_round(o[i], id, dq);
-            }
-            const int q0 = qb * kAttQ;
-            uint32_t pk[16];
-#pragma unroll
-            for (int i = 0; i < 16; i++) pk[i] = pack_h2(o[2 * i], o[2 * i + 1]);
-            store_rows64(stage + warp * 2048, pk, out + (size_t)(t0 + q0 + quad * 32) * d + (size_t)head * DH + g * 32, (size_t)d, L - q0 - quad * 32, lane);
-        };
-
         float mx_next = -INFINITY;
-        for (int c = 0; c < nc; c++) mx_next = step_a(c, mx_next);  // pass A of block 0 (not overlapped)
+        for (int c = 0; c < nc; c++) mx_next = step_a(c, mx_next, (uint32_t)((c + 2) % 3));  // pass A of block 0 (not overlapped)
         for (int qb = 0; qb < nqb; qb++) {
             // ---- row maximum of this block over the four groups
             float mx = mx_next;
@@ -361,15 +376,13 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
             }
             mx *= scale;  // max(s*scale) == max(s)*scale for scale > 0 (rounding is monotonic)
             mx_next = -INFINITY;
-            // the previous block's O: read before this block's first P is handed over (the MMA on it overwrites O); the groups
-            // that read O (0 .. dh/32 - 1) belong to the first 64-key half, whose P the first MMA of the block waits for
-            if (qb > 0) epilogue(qb - 1);
             BK_TR(tw, 12);
             for (int c = 0; c < nc; c++) {
                 // ---- pass B job: p = f16(exp(f16(s*scale - max))) for my 32 keys of chunk c, written back over the scores
                 const uint32_t slot = nb & 1;
                 BK_TR(tw, 1);
-                mbar_wait(&sfull[slot], (nb >> 1) & 1);
+                mbar_wait(&sfull[slot], (spar >> slot) & 1);
+                spar ^= 1u << slot;
                 BK_TR(tw, 2);
                 tc_fence_after();
                 const int key0 = c * kStreamKeys + g * 32;
@@ -394,12 +407,8 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                             x = __fadd2_rn(make_float2(__fmul_rn(__uint_as_float(a[i]), scale), __fmul_rn(__uint_as_float(a[i + 1]), scale)), nmx2);
                         const float2 z = __fmul2_rn(__half22float2(__floats2half2_rn(x.x, x.y)), l2e);
                         float2 e;
-#ifdef BK_EXP_NOEXP
-                        e = z;
-#else
                         asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(z.x));
                         asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(z.y));
-#endif
                         const __half2 hp = __floats2half2_rn(e.x, e.y);
                         pk[i >> 1] = *reinterpret_cast<const uint32_t *>(&hp);
                     }
@@ -414,17 +423,16 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                 BK_TR(tw, 6);
                 nb++;
                 // ---- pass A job of the next block, same chunk
-                if (qb + 1 < nqb) mx_next = step_a(c, mx_next);
+                if (qb + 1 < nqb) mx_next = step_a(c, mx_next, 2u);
             }
         }
-        epilogue(nqb - 1);
     }
     BK_TR(tw, 14);
 
     tc_fence_before();
     __syncthreads();
     BK_TR(tw, 15);
-    if (warp == CW) {
+    if (warp == CW + 1) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }
@@ -445,6 +453,6 @@ static cudaError_t launch_att_pt(const CUtensorMap &tm, const int32_t *cu, int n
     }
     dim3 grid(1, n_head, n_seq);
     const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934
-    LaunchConfig lc(grid, dim3(kStreamThreads), smem, st);
+    LaunchConfig lc(grid, dim3(kPtThreads), smem, st);
     return cudaLaunchKernelEx(&lc.cfg, attention_pt_kernel<DH>, tm, cu, d, out, qmode, scale);
 }
