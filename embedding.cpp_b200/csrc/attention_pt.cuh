@@ -77,31 +77,41 @@ __device__ unsigned long long g_att_trace[8][1024];
 constexpr int kPtThreads = kStreamThreads + 128;  // 16 softmax warps, score warp, P.V warp, 4 output warps
 constexpr int kPtTail = 192 + 2 * 2048 + 4 * 2048;  // barriers + TMEM slot, two row-maximum exchange buffers, output staging
 
+// One (sentence, head) of the launch: item i = sentence * n_head + head.  A CTA stays on its SM and takes items
+// blockIdx.x, blockIdx.x + gridDim.x, ... (the batcher has sorted the sentences longest first, so this deals the work out evenly).
+struct PtItem {
+    int t0, L, head;   // first token row, tokens, head
+    int nqb, nc;       // 128-query blocks, 128-key score chunks per pass
+    int Lk16, Lk64;
+};
+__device__ __forceinline__ PtItem pt_item(int t0, int L, int head) {
+    PtItem it;
+    it.t0 = t0; it.L = L; it.head = head;
+    it.nqb = (L + kAttQ - 1) / kAttQ;
+    it.nc = (L + kStreamKeys - 1) / kStreamKeys;
+    it.Lk16 = (L + 15) & ~15;
+    it.Lk64 = (L + 63) & ~63;
+    return it;
+}
+
 template <int DH>
 __global__ void __launch_bounds__(kPtThreads, 1)
-attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__restrict__ cu, int d, __half *__restrict__ out,
-                    int qmode, float scale) {
+attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__restrict__ cu, int n_items, int n_head, int lk_max, int d,
+                    __half *__restrict__ out, int qmode, float scale) {
     constexpr int ROWB = DH * 2;
-    constexpr int CW = 16;                 // score warp (TMA, S MMAs, TMEM allocation); CW + 1: P.V warp
+    constexpr int CW = 16;                 // score warp (TMA, S MMAs); CW + 1: P.V warp (TMEM allocation); CW + 2 .. CW + 5: output warps
     constexpr uint32_t kOCol = 3 * kStreamKeys;            // O [384, 384+dh) | row sums [384+dh, +16)
     extern __shared__ __align__(1024) uint8_t att_raw[];
     uint8_t *smem = att_raw;
 
     pdl_launch_dependents();
     pdl_wait();  // the sequence bounds are read first thing
-    const int seq = blockIdx.z, head = blockIdx.y;
-    const int t0 = __ldg(cu + seq);
-    const int L = __ldg(cu + seq + 1) - t0;
-    if (L <= 0) return;
-    const int nqb = (L + kAttQ - 1) / kAttQ;
-    const int Lk16 = (L + 15) & ~15;
-    const int Lk64 = (L + 63) & ~63;
-    const int nc = (L + kStreamKeys - 1) / kStreamKeys;  // score chunks per pass
 
+    // the layout is that of the longest sentence of the launch (lk_max = its length rounded up to 64)
     uint8_t *sQ = smem;                          // [2][128 rows]
     uint8_t *sK = sQ + kStreamQ * kAttQ * ROWB;
-    uint8_t *sV = sK + Lk64 * ROWB;
-    uint8_t *sOnes = sV + Lk64 * ROWB;           // 16 keys x ROWB of f16 1.0: the second MN atom of every P.V step
+    uint8_t *sV = sK + lk_max * ROWB;
+    uint8_t *sOnes = sV + lk_max * ROWB;         // 16 keys x ROWB of f16 1.0: the second MN atom of every P.V step
     uint8_t *tail = sOnes + 16 * ROWB;
     uint64_t *bar_q = reinterpret_cast<uint64_t *>(tail);  // [2] Q buffer landed
     uint64_t *bar_v = bar_q + 2;
@@ -119,11 +129,45 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #ifdef BK_EXP_TRACE
-    const bool trace_on = blockIdx.z == 64 && blockIdx.y == 0;
+    const bool trace_on = blockIdx.x == 5;
     int tr_n = 0;
     const int tw = warp == 20 ? 6 : warp >= CW + 2 ? 7 : warp >= CW ? 4 + (warp - CW) : warp == 0 ? 0 : warp == 5 ? 1 : warp == 10 ? 2 : warp == 15 ? 3 : 7;
     BK_TR(tw, 0);
 #endif
+    // every warp walks the same item list; the bounds of the next item are fetched one item ahead
+    const int item0 = (int)blockIdx.x, istep = (int)gridDim.x;
+    auto fetch = [&](int i, int &t0, int &L) {
+        if (i < n_items) { const int s = i / n_head; t0 = __ldg(cu + s); L = __ldg(cu + s + 1) - t0; } else { t0 = 0; L = 0; }
+    };
+    int nx_t0, nx_L;
+    fetch(item0, nx_t0, nx_L);
+
+    // Q(0), Q(1) and K of an item (score warp), V of an item (score warp for the first item, afterwards the P.V warp)
+    auto load_qk = [&](const PtItem &it) {
+        const int cq = it.head * DH, ck = d + it.head * DH;
+        const int n_box = it.Lk64 >> 6;
+        mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
+        tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, it.t0);
+        tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, it.t0 + 64);
+        for (int c = 0; c < it.nc; c++) {  // K in chunks of 128 keys (two 64-row boxes, the last chunk possibly one)
+            const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
+            mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
+            for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, it.t0 + (2 * c + b) * 64);
+        }
+        if (it.nqb > 1) {
+            uint8_t *q1 = sQ + kAttQ * ROWB;
+            mbar_expect_tx_e(&bar_q[1], (uint32_t)(kAttQ * ROWB));
+            tma_load_2d_e(q1, &tmQKV, &bar_q[1], cq, it.t0 + kAttQ);
+            tma_load_2d_e(q1 + 64 * ROWB, &tmQKV, &bar_q[1], cq, it.t0 + kAttQ + 64);
+        }
+    };
+    auto load_v = [&](const PtItem &it) {
+        const int cv = 2 * d + it.head * DH;
+        const int n_box = it.Lk64 >> 6;
+        mbar_expect_tx_e(bar_v, (uint32_t)(it.Lk64 * ROWB));
+        for (int c = 0; c < n_box; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, it.t0 + c * 64);
+    };
+
     if (warp == CW) {
         if (lane == 0) {
             tma_prefetch_desc(&tmQKV);
@@ -135,27 +179,10 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
             mbar_fence_init();
         }
         __syncwarp();
-        {
-            // the loads first (they need the barriers only): their latency runs under the TMEM allocation and the CTA-wide sync
-            const int cq = head * DH, ck = d + head * DH, cv = 2 * d + head * DH;
-            const int n_box = Lk64 >> 6;
-            mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
-            tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, t0);
-            tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, t0 + 64);
-            for (int c = 0; c < nc; c++) {  // K in chunks of 128 keys (two 64-row boxes, the last chunk possibly one)
-                const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
-                mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
-                for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, t0 + (2 * c + b) * 64);
-            }
-            if (nqb > 1) {
-                uint8_t *q1 = sQ + kAttQ * ROWB;
-                mbar_expect_tx_e(&bar_q[1], (uint32_t)(kAttQ * ROWB));
-                tma_load_2d_e(q1, &tmQKV, &bar_q[1], cq, t0 + kAttQ);
-                tma_load_2d_e(q1 + 64 * ROWB, &tmQKV, &bar_q[1], cq, t0 + kAttQ + 64);
-            }
-            mbar_expect_tx_e(bar_v, (uint32_t)(Lk64 * ROWB));
-            for (int c = 0; c < n_box; c++) tma_load_2d_e(sV + c * 64 * ROWB, &tmQKV, bar_v, cv, t0 + c * 64);
-        }
+        // the first item's loads (they need the barriers only): their latency runs under the TMEM allocation and the CTA-wide sync
+        const PtItem it = pt_item(nx_t0, nx_L, item0 % n_head);
+        load_qk(it);
+        load_v(it);
     } else if (warp == CW + 1) {  // meanwhile: the all-ones tile and the TMEM allocation
         for (int i = lane; i < 16 * ROWB / 4; i += 32) reinterpret_cast<uint32_t *>(sOnes)[i] = 0x3C003C00u;
         fence_proxy_async_smem();
@@ -170,154 +197,188 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
 
     if (warp == CW) {
         // ================================================================ score warp: TMA loads, S = Q . K^T jobs
-        const int cq = head * DH;  // (Q(0), Q(1), K and V were requested in the prologue)
-        auto load_q = [&](int qb) {  // query block qb -> Q buffer qb % 2
-            uint8_t *q = sQ + (qb % kStreamQ) * kAttQ * ROWB;
-            uint64_t *bar = &bar_q[qb % kStreamQ];
-            mbar_expect_tx_e(bar, (uint32_t)(kAttQ * ROWB));
-            tma_load_2d_e(q, &tmQKV, bar, cq, t0 + qb * kAttQ);
-            tma_load_2d_e(q + 64 * ROWB, &tmQKV, bar, cq, t0 + qb * kAttQ + 64);
-        };
-
-        // score jobs in the order the softmax warps consume them: A(0,0..nc-1), then B(q,c) A(q+1,c) for c = 0..nc-1, q = 0..
-        // Slots: pass B of chunk number b -> slot b % 2, pass A -> slot 2; the prologue A(0,c), which has the ring to itself, cycles
-        // through all three (c -> (c + 2) % 3) so that its MMAs do not wait for the round trip of one slot.
-        const int n_jobs = 2 * nqb * nc;
-        uint32_t used = 0, par = 0;       // per slot (bit): has been used / number of uses so far is odd
+        // Score jobs of an item in the order the softmax warps consume them: A(0,0..nc-1), then B(q,c) A(q+1,c) for c = 0..nc-1, q = 0..
+        // Slots: pass B of chunk number b (counted over the whole CTA) -> slot b % 2, pass A -> slot 2; the prologue A(0,c), which has
+        // the ring to itself, cycles through all three (c -> (c + 2) % 3) so that its MMAs do not wait for the round trip of one slot.
+        uint32_t used = 0, par = 0;       // per score slot (bit): has been used / number of uses so far is odd
+        uint32_t kpar = 0, qpar = 0;      // per K-chunk / Q-buffer barrier (bit): parity of the next phase to wait for
         uint32_t nbj = 0;                 // pass-B jobs issued
-        bool prologue = true, job_a = true;
-        int jq = 0, jc = 0;               // B jobs: block jq, chunk jc; A jobs: block jq + 1 (block 0 in the prologue), chunk jc
         const uint64_t dk0 = umma_desc_kmajor<ROWB>(smem_u32(sK));
         const uint64_t dq0 = umma_desc_kmajor<ROWB>(smem_u32(sQ));
-        for (int js = 0; js < n_jobs; js++) {
-            BK_TR(tw, 20);
-            if (js < nc) mbar_wait(&bar_k[js], 0);  // prologue job A(0, js): the first user of key chunk js
-            const uint32_t slot = prologue ? (uint32_t)((js + 2) % 3) : job_a ? 2u : (nbj & 1);
-            // the previous contents have been consumed: slot 2 and the prologue's slots -- in the registers of all 16 warps; a pass-B
-            // slot -- the MMAs that read its P have retired
-            if ((used >> slot) & 1) mbar_wait(&sfree[slot], ((par >> slot) & 1) ^ 1);
-            used |= 1u << slot;
-            par ^= 1u << slot;
-            if (!job_a) nbj++;
-            const int blk = job_a ? (prologue ? 0 : jq + 1) : jq;
-            if (job_a && jc == 0) mbar_wait(&bar_q[blk % kStreamQ], (uint32_t)((blk / kStreamQ) & 1));  // first use of Q(blk)
-            BK_TR(tw, 21);
-            const int n0 = jc * kStreamKeys;
-            const int nn = Lk16 - n0 < kStreamKeys ? Lk16 - n0 : kStreamKeys;
-            const uint64_t dq = dq0 + (uint64_t)(((blk % kStreamQ) * kAttQ * ROWB) >> 4);
-            const uint64_t dk = dk0 + (uint64_t)((n0 * ROWB) >> 4);
-            const uint32_t idesc = att_idesc((uint32_t)nn, 0);
-            tc_fence_after();
-#pragma unroll
-            for (int k = 0; k < DH / 16; k++)
-                umma_f16_e<1>(tmem_base + slot * kStreamKeys, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
-            umma_commit_e<1>(&sfull[slot]);
-            BK_TR(tw, 22);
-            if (prologue) {
-                if (++jc == nc) { prologue = false; job_a = false; jc = 0; }
-            } else if (!job_a) {
-                if (jq + 1 < nqb) job_a = true;
-                else if (++jc == nc) { jc = 0; jq++; }
-            } else {
-                job_a = false;
-                if (++jc == nc) {
-                    // A(jq + 1, nc - 1) was the last job of this round; the one before it, B(jq, nc - 1), the last reader of Q(jq).
-                    // Refill that buffer with Q(jq + 2) now, a whole round of pass-B jobs before its first use.
-                    if (jq + 2 < nqb) {
-                        const uint32_t lbs = (nbj - 1) & 1;  // slot of B(jq, nc - 1): its latest use
-                        mbar_wait(&sfull[lbs], ((par >> lbs) & 1) ^ 1);
-                        load_q(jq + 2);
-                    }
-                    jc = 0; jq++;
+        for (int item = item0; item < n_items; item += istep) {
+            const PtItem it = pt_item(nx_t0, nx_L, item % n_head);
+            fetch(item + istep, nx_t0, nx_L);
+            BK_TR(tw, 19);
+            const int cq = it.head * DH;
+            const int nqb = it.nqb, nc = it.nc;
+            const int n_jobs = 2 * nqb * nc;
+            bool prologue = true, job_a = true;
+            int jq = 0, jc = 0;               // B jobs: block jq, chunk jc; A jobs: block jq + 1 (block 0 in the prologue), chunk jc
+            uint32_t last_slot = 0;
+            for (int js = 0; js < n_jobs; js++) {
+                BK_TR(tw, 20);
+                if (js < nc) { mbar_wait(&bar_k[js], (kpar >> js) & 1); kpar ^= 1u << js; }  // prologue job A(0, js): the first user of key chunk js
+                const uint32_t slot = prologue ? (uint32_t)((js + 2) % 3) : job_a ? 2u : (nbj & 1);
+                // the previous contents have been consumed: slot 2 and the prologue's slots -- in the registers of all 16 warps; a pass-B
+                // slot -- the MMAs that read its P have retired
+                if ((used >> slot) & 1) mbar_wait(&sfree[slot], ((par >> slot) & 1) ^ 1);
+                used |= 1u << slot;
+                par ^= 1u << slot;
+                last_slot = slot;
+                if (!job_a) nbj++;
+                const int blk = job_a ? (prologue ? 0 : jq + 1) : jq;
+                if (job_a && jc == 0) {  // first use of Q(blk)
+                    const uint32_t qb2 = (uint32_t)(blk % kStreamQ);
+                    mbar_wait(&bar_q[qb2], (qpar >> qb2) & 1);
+                    qpar ^= 1u << qb2;
                 }
+                BK_TR(tw, 21);
+                const int n0 = jc * kStreamKeys;
+                const int nn = it.Lk16 - n0 < kStreamKeys ? it.Lk16 - n0 : kStreamKeys;
+                const uint64_t dq = dq0 + (uint64_t)(((blk % kStreamQ) * kAttQ * ROWB) >> 4);
+                const uint64_t dk = dk0 + (uint64_t)((n0 * ROWB) >> 4);
+                const uint32_t idesc = att_idesc((uint32_t)nn, 0);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < DH / 16; k++)
+                    umma_f16_e<1>(tmem_base + slot * kStreamKeys, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
+                umma_commit_e<1>(&sfull[slot]);
+                BK_TR(tw, 22);
+                if (prologue) {
+                    if (++jc == nc) { prologue = false; job_a = false; jc = 0; }
+                } else if (!job_a) {
+                    if (jq + 1 < nqb) job_a = true;
+                    else if (++jc == nc) { jc = 0; jq++; }
+                } else {
+                    job_a = false;
+                    if (++jc == nc) {
+                        // A(jq + 1, nc - 1) was the last job of this round; the one before it, B(jq, nc - 1), the last reader of Q(jq).
+                        // Refill that buffer with Q(jq + 2) now, a whole round of pass-B jobs before its first use.
+                        if (jq + 2 < nqb) {
+                            const uint32_t lbs = (nbj - 1) & 1;  // slot of B(jq, nc - 1): its latest use
+                            mbar_wait(&sfull[lbs], ((par >> lbs) & 1) ^ 1);
+                            uint8_t *q = sQ + (jq % kStreamQ) * kAttQ * ROWB;
+                            uint64_t *bar = &bar_q[jq % kStreamQ];
+                            mbar_expect_tx_e(bar, (uint32_t)(kAttQ * ROWB));
+                            tma_load_2d_e(q, &tmQKV, bar, cq, it.t0 + (jq + 2) * kAttQ);
+                            tma_load_2d_e(q + 64 * ROWB, &tmQKV, bar, cq, it.t0 + (jq + 2) * kAttQ + 64);
+                        }
+                        jc = 0; jq++;
+                    }
+                }
+            }
+            // the next item's Q(0), Q(1) and K: as soon as the last score MMAs of this item (and with them all earlier ones) have
+            // retired, i.e. under the last chunk's exponentials, its P.V MMAs and the output of the last block
+            if (item + istep < n_items) {
+                mbar_wait(&sfull[last_slot], ((par >> last_slot) & 1) ^ 1);
+                load_qk(pt_item(nx_t0, nx_L, (item + istep) % n_head));
             }
         }
     } else if (warp == CW + 1) {
-        // ================================================================ P.V warp: O += P . V, rowsum += P . 1, P read from the score slot
-        // one MMA per 16 keys: [O | row sums] += P . [V | 1], N = dh + 16 (the row sums come out of the same instruction)
+        // ================================================================ P.V warp: [O | row sums] += P . [V | 1], P read from the score slot
+        // one MMA per 16 keys, N = dh + 16: the row sums come out of the same instruction
         const uint32_t idesc_pv = att_idesc(DH + kSumCols, 1);
         const uint32_t v0 = smem_u32(sV), o1 = smem_u32(sOnes);
         uint32_t ppar = 0;  // per pass-B slot (bit): number of hand-overs so far is odd
-        // the prologue's chunks 1 and 2 went through the pass-B slots 0 and 1: the 16 warps report "read" on the P barriers, and the
-        // slot is handed back the way it always is -- by a commit from this warp (nothing outstanding: it arrives at once)
-        for (int c = 1; c < nc && c < 3; c++) {
-            const uint32_t slot = (uint32_t)(c - 1);
-            mbar_wait(&pfull[slot * 2], 0);
-            mbar_wait(&pfull[slot * 2 + 1], 0);
-            umma_commit_e<1>(&sfree[slot]);
-            ppar ^= 1u << slot;
-        }
-        mbar_wait(bar_v, 0);
         uint32_t pv_b = 0;  // pass-B jobs consumed
-        for (int qb = 0; qb < nqb; qb++) {
-            for (int c = 0; c < nc; c++, pv_b++) {
-                const uint32_t slot = pv_b & 1;
-                for (int sub = 0; sub < 2; sub++) {
-                    BK_TR(tw, 30 + sub);
-                    mbar_wait(&pfull[slot * 2 + sub], (ppar >> slot) & 1);
-                    if (qb > 0 && (c | sub) == 0) mbar_wait(ofree, (uint32_t)((qb - 1) & 1));  // the first MMA of a block overwrites O
-                    BK_TR(tw, 32 + sub);
-                    tc_fence_after();
-                    const int key0 = c * kStreamKeys + sub * 64;
-                    const int rem = Lk16 - key0;
-                    const int ksteps = rem >= 64 ? 4 : rem > 0 ? rem >> 4 : 0;
-                    const uint32_t pa = tmem_base + slot * kStreamKeys + (uint32_t)(sub * 64);  // keys 16 ks ..: group 2 sub + ks / 2, its columns 8 (ks % 2) ..
-                    for (int ks = 0; ks < ksteps; ks++) {
-                        const uint32_t va = v0 + (uint32_t)((key0 + 16 * ks) * ROWB);
-                        umma_f16_ts_e(tmem_base + kOCol, pa + (uint32_t)((ks >> 1) * 32 + (ks & 1) * 8), umma_desc_mnmajor_ones<ROWB>(va, o1 - va), idesc_pv,
-                                      (c | sub | ks) != 0);
-                    }
-                }
+        uint32_t gb = 0;    // query blocks done by this CTA
+        uint32_t vpar = 0;
+        for (int item = item0; item < n_items; item += istep) {
+            const PtItem it = pt_item(nx_t0, nx_L, item % n_head);
+            fetch(item + istep, nx_t0, nx_L);
+            BK_TR(tw, 19);
+            // the prologue's chunks 1 and 2 went through the pass-B slots: the 16 warps report "read" on the P barriers, and the slot is
+            // handed back the way it always is -- by a commit from this warp (nothing outstanding on it: it arrives at once)
+            for (int c = 1; c < it.nc && c < 3; c++) {
+                const uint32_t slot = (uint32_t)((c + 2) % 3);
+                mbar_wait(&pfull[slot * 2], (ppar >> slot) & 1);
+                mbar_wait(&pfull[slot * 2 + 1], (ppar >> slot) & 1);
                 umma_commit_e<1>(&sfree[slot]);
                 ppar ^= 1u << slot;
-                BK_TR(tw, 34);
             }
-            umma_commit_e<1>(bar_o);
+            mbar_wait(bar_v, vpar);
+            vpar ^= 1;
+            for (int qb = 0; qb < it.nqb; qb++, gb++) {
+                for (int c = 0; c < it.nc; c++, pv_b++) {
+                    const uint32_t slot = pv_b & 1;
+                    for (int sub = 0; sub < 2; sub++) {
+                        BK_TR(tw, 30 + sub);
+                        mbar_wait(&pfull[slot * 2 + sub], (ppar >> slot) & 1);
+                        if (gb > 0 && (c | sub) == 0) mbar_wait(ofree, (gb - 1) & 1);  // the first MMA of a block overwrites O
+                        BK_TR(tw, 32 + sub);
+                        tc_fence_after();
+                        const int key0 = c * kStreamKeys + sub * 64;
+                        const int rem = it.Lk16 - key0;
+                        const int ksteps = rem >= 64 ? 4 : rem > 0 ? rem >> 4 : 0;
+                        const uint32_t pa = tmem_base + slot * kStreamKeys + (uint32_t)(sub * 64);  // keys 16 ks ..: group 2 sub + ks / 2, its columns 8 (ks % 2) ..
+                        for (int ks = 0; ks < ksteps; ks++) {
+                            const uint32_t va = v0 + (uint32_t)((key0 + 16 * ks) * ROWB);
+                            umma_f16_ts_e(tmem_base + kOCol, pa + (uint32_t)((ks >> 1) * 32 + (ks & 1) * 8), umma_desc_mnmajor_ones<ROWB>(va, o1 - va), idesc_pv,
+                                          (c | sub | ks) != 0);
+                        }
+                    }
+                    umma_commit_e<1>(&sfree[slot]);
+                    ppar ^= 1u << slot;
+                    BK_TR(tw, 34);
+                }
+                umma_commit_e<1>(bar_o);
+            }
+            // the next item's V: when this item's last P.V MMAs have retired (the first P of the next item is a prologue and a chunk
+            // of exponentials away)
+            if (item + istep < n_items) {
+                mbar_wait(bar_o, (gb - 1) & 1);
+                load_v(pt_item(nx_t0, nx_L, (item + istep) % n_head));
+            }
         }
     } else if (warp >= CW + 2) {
         // ======================================================================= output warps: O * (1 / sum p) -> out rows
-        // One warp per TMEM lane quarter.  The softmax warps never touch O: while they are in the next block's first chunk, these
-        // warps take the finished block out of tensor memory (the P.V warp's first MMA of that block waits for `ofree`), scale,
-        // quantise for Q4 models and store.
+        // One warp per TMEM lane quarter.  The softmax warps never touch O: while they are in the next block's first chunk (or the
+        // next item's prologue), these warps take the finished block out of tensor memory (the P.V warp's first MMA of the next
+        // block waits for `ofree`), scale, quantise for Q4 models and store.
         const int quad = warp & 3;
         const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
         uint8_t *st = stage + (warp - (CW + 2)) * 2048;
-        for (int qb = 0; qb < nqb; qb++) {
-            mbar_wait(bar_o, (uint32_t)(qb & 1));
-            BK_TR(tw, 16);
-            tc_fence_after();
-            const float sum = __uint_as_float(tmem_ld_32x1(tlane + kOCol + (uint32_t)DH));
-            const float inv = 1.0f / sum;
-            const int row0 = qb * kAttQ + quad * 32;
+        uint32_t gb = 0;  // query blocks done by this CTA
+        for (int item = item0; item < n_items; item += istep) {
+            const PtItem it = pt_item(nx_t0, nx_L, item % n_head);
+            fetch(item + istep, nx_t0, nx_L);
+            for (int qb = 0; qb < it.nqb; qb++, gb++) {
+                mbar_wait(bar_o, gb & 1);
+                BK_TR(tw, 16);
+                tc_fence_after();
+                const float sum = __uint_as_float(tmem_ld_32x1(tlane + kOCol + (uint32_t)DH));
+                const float inv = 1.0f / sum;
+                const int row0 = qb * kAttQ + quad * 32;
 #pragma unroll
-            for (int hf = 0; hf < DH / 32; hf++) {
-                uint32_t a[32];
-                tmem_ld_32x32(tlane + kOCol + (uint32_t)(hf * 32), a);
-                tmem_ld_wait();
-                if (hf == DH / 32 - 1) {  // all of O is in registers (the P.V warp is at least a chunk of exponentials away from needing it)
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(ofree);
-                    BK_TR(tw, 17);
+                for (int hf = 0; hf < DH / 32; hf++) {
+                    uint32_t a[32];
+                    tmem_ld_32x32(tlane + kOCol + (uint32_t)(hf * 32), a);
+                    tmem_ld_wait();
+                    if (hf == DH / 32 - 1) {  // all of O is in registers (the P.V warp is at least a chunk of exponentials away from needing it)
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(ofree);
+                        BK_TR(tw, 17);
+                    }
+                    float o[32];
+#pragma unroll
+                    for (int i = 0; i < 32; i++) o[i] = __uint_as_float(a[i]) * inv;
+                    if (qmode) {  // the attention-output GEMM of a Q4 model quantises its input per 32 features (ggml.c:9493-9509)
+                        float amax = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 32; i++) amax = fmaxf(amax, fabsf(o[i]));
+                        float id, dq;
+                        q8_scales(amax, qmode, id, dq);
+#pragma unroll
+                        for (int i = 0; i < 32; i++) o[i] = q8_round(o[i], id, dq);
+                    }
+                    uint32_t pk[16];
+#pragma unroll
+                    for (int i = 0; i < 16; i++) pk[i] = pack_h2(o[2 * i], o[2 * i + 1]);
+                    store_rows64(st, pk, out + (size_t)(it.t0 + row0) * d + (size_t)it.head * DH + hf * 32, (size_t)d, it.L - row0, lane);
                 }
-                float o[32];
-#pragma unroll
-                for (int i = 0; i < 32; i++) o[i] = __uint_as_float(a[i]) * inv;
-                if (qmode) {  // the attention-output GEMM of a Q4 model quantises its input per 32 features (ggml.c:9493-9509)
-                    float amax = 0.f;
-#pragma unroll
-                    for (int i = 0; i < 32; i++) amax = fmaxf(amax, fabsf(o[i]));
-                    float id, dq;
-                    q8_scales(amax, qmode, id, dq);
-#pragma unroll
-                    for (int i = 0; i < 32; i++) o[i] = q8_round(o[i], id, dq);
-                }
-                uint32_t pk[16];
-#pragma unroll
-                for (int i = 0; i < 16; i++) pk[i] = pack_h2(o[2 * i], o[2 * i + 1]);
-                store_rows64(st, pk, out + (size_t)(t0 + row0) * d + (size_t)head * DH + hf * 32, (size_t)d, L - row0, lane);
+                BK_TR(tw, 18);
             }
-            BK_TR(tw, 18);
         }
     } else {
         // ======================================================================= softmax warps
@@ -328,102 +389,109 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         const int psub = g >> 1;                              // my 64-key half of a chunk
         uint32_t spar = 0;                                    // per score slot (bit): number of chunks consumed from it so far is odd
         uint32_t nb = 0;                                      // pass-B jobs done
+        uint32_t gb = 0;                                      // query blocks done by this CTA
+        for (int item = item0; item < n_items; item += istep) {
+            const PtItem it = pt_item(nx_t0, nx_L, item % n_head);
+            fetch(item + istep, nx_t0, nx_L);
+            BK_TR(tw, 19);
+            const int L = it.L, nc = it.nc, nqb = it.nqb;
 
-        // one pass-A job: fold this group's 32 keys of chunk c into the running row maximum
-        auto step_a = [&](int c, float mx, uint32_t slot) {
-            BK_TR(tw, 7);
-            mbar_wait(&sfull[slot], (spar >> slot) & 1);
-            spar ^= 1u << slot;
-            BK_TR(tw, 8);
-            tc_fence_after();
-            const int key0 = c * kStreamKeys + g * 32;
-            if (key0 < L) {
-                uint32_t a[32];
-                tmem_ld_32x32(tcol + slot * kStreamKeys, a);
-                tmem_ld_wait();
-                const int nv = L - key0;
-                if (nv < 32) {  // keys past the sentence never enter
-#pragma unroll
-                    for (int i = 0; i < 32; i++) if (i >= nv) a[i] = 0xff800000u;
-                }
-                float m0 = mx, m1 = -INFINITY;
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                    m0 = fmaxf(m0, fmaxf(__uint_as_float(a[i]), __uint_as_float(a[i + 1])));
-                    m1 = fmaxf(m1, fmaxf(__uint_as_float(a[i + 2]), __uint_as_float(a[i + 3])));
-                }
-                mx = fmaxf(m0, m1);
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(slot == 2 ? &sfree[2] : &pfull[slot * 2 + psub]);  // (a prologue chunk in a pass-B slot: see the P.V warp)
-            BK_TR(tw, 9);
-            return mx;
-        };
-        float mx_next = -INFINITY;
-        for (int c = 0; c < nc; c++) mx_next = step_a(c, mx_next, (uint32_t)((c + 2) % 3));  // pass A of block 0 (not overlapped)
-        for (int qb = 0; qb < nqb; qb++) {
-            // ---- row maximum of this block over the four groups
-            float mx = mx_next;
-            {
-                float *rb = red + (qb & 1) * 512;
-                rb[g * 128 + r] = mx;
-                BK_TR(tw, 10);
-                named_bar_sync(1, 512);
-                BK_TR(tw, 11);
-#pragma unroll
-                for (int gg = 0; gg < 4; gg++) mx = fmaxf(mx, rb[gg * 128 + r]);
-            }
-            mx *= scale;  // max(s*scale) == max(s)*scale for scale > 0 (rounding is monotonic)
-            mx_next = -INFINITY;
-            BK_TR(tw, 12);
-            for (int c = 0; c < nc; c++) {
-                // ---- pass B job: p = f16(exp(f16(s*scale - max))) for my 32 keys of chunk c, written back over the scores
-                const uint32_t slot = nb & 1;
-                BK_TR(tw, 1);
+            // one pass-A job: fold this group's 32 keys of chunk c into the running row maximum
+            auto step_a = [&](int c, float mx, uint32_t slot) {
+                BK_TR(tw, 7);
                 mbar_wait(&sfull[slot], (spar >> slot) & 1);
                 spar ^= 1u << slot;
-                BK_TR(tw, 2);
+                BK_TR(tw, 8);
                 tc_fence_after();
                 const int key0 = c * kStreamKeys + g * 32;
-                if (key0 < L) {  // otherwise no real key: the MMA does not read these P columns
+                if (key0 < L) {
                     uint32_t a[32];
                     tmem_ld_32x32(tcol + slot * kStreamKeys, a);
                     tmem_ld_wait();
-                    BK_TR(tw, 3);
                     const int nv = L - key0;
-                    if (nv < 32) {  // s = -inf -> p = 0 exactly
+                    if (nv < 32) {  // keys past the sentence never enter
 #pragma unroll
                         for (int i = 0; i < 32; i++) if (i >= nv) a[i] = 0xff800000u;
                     }
-                    uint32_t pk[16];
-                    const float2 sc2 = make_float2(scale, scale), nmx2 = make_float2(-mx, -mx), l2e = make_float2(1.4426950408889634f, 1.4426950408889634f);
+                    float m0 = mx, m1 = -INFINITY;
 #pragma unroll
-                    for (int i = 0; i < 32; i += 2) {  // same instruction sequence as attention_tc_kernel
-                        float2 x;
-                        if (DH == 64)
-                            x = __ffma2_rn(make_float2(__uint_as_float(a[i]), __uint_as_float(a[i + 1])), sc2, nmx2);
-                        else
-                            x = __fadd2_rn(make_float2(__fmul_rn(__uint_as_float(a[i]), scale), __fmul_rn(__uint_as_float(a[i + 1]), scale)), nmx2);
-                        const float2 z = __fmul2_rn(__half22float2(__floats2half2_rn(x.x, x.y)), l2e);
-                        float2 e;
-                        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(z.x));
-                        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(z.y));
-                        const __half2 hp = __floats2half2_rn(e.x, e.y);
-                        pk[i >> 1] = *reinterpret_cast<const uint32_t *>(&hp);
+                    for (int i = 0; i < 32; i += 4) {
+                        m0 = fmaxf(m0, fmaxf(__uint_as_float(a[i]), __uint_as_float(a[i + 1])));
+                        m1 = fmaxf(m1, fmaxf(__uint_as_float(a[i + 2]), __uint_as_float(a[i + 3])));
                     }
-                    BK_TR(tw, 4);
-                    tmem_st_32x16(tcol + slot * kStreamKeys, pk);
-                    tmem_st_wait();
-                    BK_TR(tw, 5);
+                    mx = fmaxf(m0, m1);
                 }
-                tc_fence_before();  // P in tensor memory -> visible to the MMAs issued behind the barrier
+                tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&pfull[slot * 2 + psub]);
-                BK_TR(tw, 6);
-                nb++;
-                // ---- pass A job of the next block, same chunk
-                if (qb + 1 < nqb) mx_next = step_a(c, mx_next, 2u);
+                if (lane == 0) mbar_arrive(slot == 2 ? &sfree[2] : &pfull[slot * 2 + psub]);  // (a prologue chunk in a pass-B slot: see the P.V warp)
+                BK_TR(tw, 9);
+                return mx;
+            };
+
+            float mx_next = -INFINITY;
+            for (int c = 0; c < nc; c++) mx_next = step_a(c, mx_next, (uint32_t)((c + 2) % 3));  // pass A of block 0 (not overlapped)
+            for (int qb = 0; qb < nqb; qb++, gb++) {
+                // ---- row maximum of this block over the four groups
+                float mx = mx_next;
+                {
+                    float *rb = red + (gb & 1) * 512;
+                    rb[g * 128 + r] = mx;
+                    BK_TR(tw, 10);
+                    named_bar_sync(1, 512);
+                    BK_TR(tw, 11);
+#pragma unroll
+                    for (int gg = 0; gg < 4; gg++) mx = fmaxf(mx, rb[gg * 128 + r]);
+                }
+                mx *= scale;  // max(s*scale) == max(s)*scale for scale > 0 (rounding is monotonic)
+                mx_next = -INFINITY;
+                for (int c = 0; c < nc; c++) {
+                    // ---- pass B job: p = f16(exp(f16(s*scale - max))) for my 32 keys of chunk c, written back over the scores
+                    const uint32_t slot = nb & 1;
+                    BK_TR(tw, 1);
+                    mbar_wait(&sfull[slot], (spar >> slot) & 1);
+                    spar ^= 1u << slot;
+                    BK_TR(tw, 2);
+                    tc_fence_after();
+                    const int key0 = c * kStreamKeys + g * 32;
+                    if (key0 < L) {  // otherwise no real key: the MMA does not read these P columns
+                        uint32_t a[32];
+                        tmem_ld_32x32(tcol + slot * kStreamKeys, a);
+                        tmem_ld_wait();
+                        BK_TR(tw, 3);
+                        const int nv = L - key0;
+                        if (nv < 32) {  // s = -inf -> p = 0 exactly
+#pragma unroll
+                            for (int i = 0; i < 32; i++) if (i >= nv) a[i] = 0xff800000u;
+                        }
+                        uint32_t pk[16];
+                        const float2 sc2 = make_float2(scale, scale), nmx2 = make_float2(-mx, -mx), l2e = make_float2(1.4426950408889634f, 1.4426950408889634f);
+#pragma unroll
+                        for (int i = 0; i < 32; i += 2) {  // same instruction sequence as attention_tc_kernel
+                            float2 x;
+                            if (DH == 64)
+                                x = __ffma2_rn(make_float2(__uint_as_float(a[i]), __uint_as_float(a[i + 1])), sc2, nmx2);
+                            else
+                                x = __fadd2_rn(make_float2(__fmul_rn(__uint_as_float(a[i]), scale), __fmul_rn(__uint_as_float(a[i + 1]), scale)), nmx2);
+                            const float2 z = __fmul2_rn(__half22float2(__floats2half2_rn(x.x, x.y)), l2e);
+                            float2 e;
+                            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(z.x));
+                            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(z.y));
+                            const __half2 hp = __floats2half2_rn(e.x, e.y);
+                            pk[i >> 1] = *reinterpret_cast<const uint32_t *>(&hp);
+                        }
+                        BK_TR(tw, 4);
+                        tmem_st_32x16(tcol + slot * kStreamKeys, pk);
+                        tmem_st_wait();
+                        BK_TR(tw, 5);
+                    }
+                    tc_fence_before();  // P in tensor memory -> visible to the MMAs issued behind the barrier
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&pfull[slot * 2 + psub]);
+                    BK_TR(tw, 6);
+                    nb++;
+                    // ---- pass A job of the next block, same chunk
+                    if (qb + 1 < nqb) mx_next = step_a(c, mx_next, 2u);
+                }
             }
         }
     }
@@ -444,15 +512,24 @@ static cudaError_t launch_att_pt(const CUtensorMap &tm, const int32_t *cu, int n
     const int Lk64 = (max_len + 63) & ~63;
     const size_t smem = (size_t)kStreamQ * kAttQ * DH * 2 + (size_t)2 * Lk64 * DH * 2 + 16 * DH * 2 + kPtTail;
     static std::atomic<bool> attr_set[64];
+    static std::atomic<int> n_sm[64];
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!attr_set[dev]) {
         cudaError_t err = cudaFuncSetAttribute(attention_pt_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (err != cudaSuccess) return err;
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        int n = 0;
+        err = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (err != cudaSuccess) return err;
+        n_sm[dev] = n;
+        attr_set[dev] = true;
     }
-    dim3 grid(1, n_head, n_seq);
+    // one CTA per SM (tensor memory: all 512 columns), each walking over items (sentence, head)
+    const long long n_items = (long long)n_seq * n_head;
+    const int sms = n_sm[dev];
+    dim3 grid((unsigned)(n_items < sms ? n_items : sms));
     const float scale = (float)(1.0 / sqrt((double)DH));  // bert.cpp:934
     LaunchConfig lc(grid, dim3(kPtThreads), smem, st);
-    return cudaLaunchKernelEx(&lc.cfg, attention_pt_kernel<DH>, tm, cu, d, out, qmode, scale);
+    return cudaLaunchKernelEx(&lc.cfg, attention_pt_kernel<DH>, tm, cu, (int)n_items, n_head, Lk64, d, out, qmode, scale);
 }
