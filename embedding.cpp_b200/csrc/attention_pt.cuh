@@ -94,6 +94,13 @@ __device__ __forceinline__ PtItem pt_item(int t0, int L, int head) {
     return it;
 }
 
+// Chunks of the NEXT item's first maximum pass A(0,*) that run during this item's last query block (whose A slot is idle): chunk c - 1
+// behind B(last, c), once key chunk c - 1 holds the next item's keys.  Needs the next Q(0) in buffer 0 while the last block reads buffer 1.
+__device__ __forceinline__ int pt_ahead(const PtItem &it, const PtItem &nxt, bool more) {
+    if (!more || !((it.nqb - 1) & 1) || it.nc < 2) return 0;
+    return it.nc - 1 < nxt.nc ? it.nc - 1 : nxt.nc;
+}
+
 template <int DH>
 __global__ void __launch_bounds__(kPtThreads, 1)
 attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__restrict__ cu, int n_items, int n_head, int lk_max, int d,
@@ -143,23 +150,21 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
     fetch(item0, nx_t0, nx_L);
 
     // Q(0), Q(1) and K of an item (score warp), V of an item (score warp for the first item, afterwards the P.V warp)
-    auto load_qk = [&](const PtItem &it) {
-        const int cq = it.head * DH, ck = d + it.head * DH;
+    auto load_q01 = [&](const PtItem &it, int b) {  // query block b (0 or 1) -> Q buffer b
+        if (b >= it.nqb) return;
+        const int cq = it.head * DH;
+        uint8_t *q = sQ + b * kAttQ * ROWB;
+        mbar_expect_tx_e(&bar_q[b], (uint32_t)(kAttQ * ROWB));
+        tma_load_2d_e(q, &tmQKV, &bar_q[b], cq, it.t0 + b * kAttQ);
+        tma_load_2d_e(q + 64 * ROWB, &tmQKV, &bar_q[b], cq, it.t0 + b * kAttQ + 64);
+    };
+    auto load_k = [&](const PtItem &it, int c) {  // keys [128 c, 128 c + 128): two 64-row boxes, the last chunk possibly one
+        if (c >= it.nc) return;
+        const int ck = d + it.head * DH;
         const int n_box = it.Lk64 >> 6;
-        mbar_expect_tx_e(&bar_q[0], (uint32_t)(kAttQ * ROWB));
-        tma_load_2d_e(sQ, &tmQKV, &bar_q[0], cq, it.t0);
-        tma_load_2d_e(sQ + 64 * ROWB, &tmQKV, &bar_q[0], cq, it.t0 + 64);
-        for (int c = 0; c < it.nc; c++) {  // K in chunks of 128 keys (two 64-row boxes, the last chunk possibly one)
-            const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
-            mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
-            for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, it.t0 + (2 * c + b) * 64);
-        }
-        if (it.nqb > 1) {
-            uint8_t *q1 = sQ + kAttQ * ROWB;
-            mbar_expect_tx_e(&bar_q[1], (uint32_t)(kAttQ * ROWB));
-            tma_load_2d_e(q1, &tmQKV, &bar_q[1], cq, it.t0 + kAttQ);
-            tma_load_2d_e(q1 + 64 * ROWB, &tmQKV, &bar_q[1], cq, it.t0 + kAttQ + 64);
-        }
+        const int boxes = n_box - 2 * c < 2 ? n_box - 2 * c : 2;
+        mbar_expect_tx_e(&bar_k[c], (uint32_t)(boxes * 64 * ROWB));
+        for (int b = 0; b < boxes; b++) tma_load_2d_e(sK + (2 * c + b) * 64 * ROWB, &tmQKV, &bar_k[c], ck, it.t0 + (2 * c + b) * 64);
     };
     auto load_v = [&](const PtItem &it) {
         const int cv = 2 * d + it.head * DH;
@@ -181,7 +186,9 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         __syncwarp();
         // the first item's loads (they need the barriers only): their latency runs under the TMEM allocation and the CTA-wide sync
         const PtItem it = pt_item(nx_t0, nx_L, item0 % n_head);
-        load_qk(it);
+        load_q01(it, 0);
+        for (int c = 0; c < 4; c++) load_k(it, c);
+        load_q01(it, 1);
         load_v(it);
     } else if (warp == CW + 1) {  // meanwhile: the all-ones tile and the TMEM allocation
         for (int i = lane; i < 16 * ROWB / 4; i += 32) reinterpret_cast<uint32_t *>(sOnes)[i] = 0x3C003C00u;
@@ -197,82 +204,97 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
 
     if (warp == CW) {
         // ================================================================ score warp: TMA loads, S = Q . K^T jobs
-        // Score jobs of an item in the order the softmax warps consume them: A(0,0..nc-1), then B(q,c) A(q+1,c) for c = 0..nc-1, q = 0..
+        // Score jobs of an item in the order the softmax warps consume them: A(0,c) for the chunks not done ahead, then B(q,c) A(q+1,c)
+        // for c = 0..nc-1, q = 0..; in the LAST query block, which has no pass A of its own, the A slot takes the next item's
+        // first block: A'(0,c-1) behind B(last,c) -- key chunk c-1 has just been refilled with the next item's keys (pt_ahead).
         // Slots: pass B of chunk number b (counted over the whole CTA) -> slot b % 2, pass A -> slot 2; the prologue A(0,c), which has
         // the ring to itself, cycles through all three (c -> (c + 2) % 3) so that its MMAs do not wait for the round trip of one slot.
         uint32_t used = 0, par = 0;       // per score slot (bit): has been used / number of uses so far is odd
         uint32_t kpar = 0, qpar = 0;      // per K-chunk / Q-buffer barrier (bit): parity of the next phase to wait for
         uint32_t nbj = 0;                 // pass-B jobs issued
+        int pre_in = 0;                   // chunks of this item's A(0,*) done during the previous item
         const uint64_t dk0 = umma_desc_kmajor<ROWB>(smem_u32(sK));
         const uint64_t dq0 = umma_desc_kmajor<ROWB>(smem_u32(sQ));
+        auto wait_k = [&](int c) { mbar_wait(&bar_k[c], (kpar >> c) & 1); kpar ^= 1u << c; };
+        auto wait_q = [&](int b) { mbar_wait(&bar_q[b], (qpar >> b) & 1); qpar ^= 1u << b; };
+        auto wait_scores = [&](uint32_t slot) { mbar_wait(&sfull[slot], ((par >> slot) & 1) ^ 1); };  // the latest job issued on `slot` has retired
+        // S[slot] = Q[qbuf] . K[chunk]^T
+        auto issue = [&](uint32_t slot, int qbuf, int chunk, int Lk16) {
+            // the previous contents have been consumed: slot 2 and the prologue's slots -- in the registers of all 16 warps; a pass-B
+            // slot -- the MMAs that read its P have retired
+            if ((used >> slot) & 1) mbar_wait(&sfree[slot], ((par >> slot) & 1) ^ 1);
+            used |= 1u << slot;
+            par ^= 1u << slot;
+            BK_TR(tw, 21);
+            const int n0 = chunk * kStreamKeys;
+            const int nn = Lk16 - n0 < kStreamKeys ? Lk16 - n0 : kStreamKeys;
+            const uint64_t dq = dq0 + (uint64_t)((qbuf * kAttQ * ROWB) >> 4);
+            const uint64_t dk = dk0 + (uint64_t)((n0 * ROWB) >> 4);
+            const uint32_t idesc = att_idesc((uint32_t)nn, 0);
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < DH / 16; k++)
+                umma_f16_e<1>(tmem_base + slot * kStreamKeys, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
+            umma_commit_e<1>(&sfull[slot]);
+            BK_TR(tw, 22);
+        };
+        int n2_t0, n2_L;  // this warp needs the next item's bounds during the current one: it fetches two items ahead
+        fetch(item0 + istep, n2_t0, n2_L);
         for (int item = item0; item < n_items; item += istep) {
             const PtItem it = pt_item(nx_t0, nx_L, item % n_head);
-            fetch(item + istep, nx_t0, nx_L);
+            nx_t0 = n2_t0; nx_L = n2_L;
+            fetch(item + 2 * istep, n2_t0, n2_L);
             BK_TR(tw, 19);
-            const int cq = it.head * DH;
+            const bool more = item + istep < n_items;
+            const PtItem nxt = pt_item(nx_t0, nx_L, (item + istep) % n_head);  // (valid if `more`)
+            const int pre_out = pt_ahead(it, nxt, more);
             const int nqb = it.nqb, nc = it.nc;
-            const int n_jobs = 2 * nqb * nc;
-            bool prologue = true, job_a = true;
-            int jq = 0, jc = 0;               // B jobs: block jq, chunk jc; A jobs: block jq + 1 (block 0 in the prologue), chunk jc
-            uint32_t last_slot = 0;
-            for (int js = 0; js < n_jobs; js++) {
+            const int cq = it.head * DH;
+            for (int c = pre_in; c < nc; c++) {  // prologue: pass A of block 0
                 BK_TR(tw, 20);
-                if (js < nc) { mbar_wait(&bar_k[js], (kpar >> js) & 1); kpar ^= 1u << js; }  // prologue job A(0, js): the first user of key chunk js
-                const uint32_t slot = prologue ? (uint32_t)((js + 2) % 3) : job_a ? 2u : (nbj & 1);
-                // the previous contents have been consumed: slot 2 and the prologue's slots -- in the registers of all 16 warps; a pass-B
-                // slot -- the MMAs that read its P have retired
-                if ((used >> slot) & 1) mbar_wait(&sfree[slot], ((par >> slot) & 1) ^ 1);
-                used |= 1u << slot;
-                par ^= 1u << slot;
-                last_slot = slot;
-                if (!job_a) nbj++;
-                const int blk = job_a ? (prologue ? 0 : jq + 1) : jq;
-                if (job_a && jc == 0) {  // first use of Q(blk)
-                    const uint32_t qb2 = (uint32_t)(blk % kStreamQ);
-                    mbar_wait(&bar_q[qb2], (qpar >> qb2) & 1);
-                    qpar ^= 1u << qb2;
-                }
-                BK_TR(tw, 21);
-                const int n0 = jc * kStreamKeys;
-                const int nn = it.Lk16 - n0 < kStreamKeys ? it.Lk16 - n0 : kStreamKeys;
-                const uint64_t dq = dq0 + (uint64_t)(((blk % kStreamQ) * kAttQ * ROWB) >> 4);
-                const uint64_t dk = dk0 + (uint64_t)((n0 * ROWB) >> 4);
-                const uint32_t idesc = att_idesc((uint32_t)nn, 0);
-                tc_fence_after();
-#pragma unroll
-                for (int k = 0; k < DH / 16; k++)
-                    umma_f16_e<1>(tmem_base + slot * kStreamKeys, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc, k != 0);
-                umma_commit_e<1>(&sfull[slot]);
-                BK_TR(tw, 22);
-                if (prologue) {
-                    if (++jc == nc) { prologue = false; job_a = false; jc = 0; }
-                } else if (!job_a) {
-                    if (jq + 1 < nqb) job_a = true;
-                    else if (++jc == nc) { jc = 0; jq++; }
-                } else {
-                    job_a = false;
-                    if (++jc == nc) {
-                        // A(jq + 1, nc - 1) was the last job of this round; the one before it, B(jq, nc - 1), the last reader of Q(jq).
-                        // Refill that buffer with Q(jq + 2) now, a whole round of pass-B jobs before its first use.
-                        if (jq + 2 < nqb) {
-                            const uint32_t lbs = (nbj - 1) & 1;  // slot of B(jq, nc - 1): its latest use
-                            mbar_wait(&sfull[lbs], ((par >> lbs) & 1) ^ 1);
-                            uint8_t *q = sQ + (jq % kStreamQ) * kAttQ * ROWB;
-                            uint64_t *bar = &bar_q[jq % kStreamQ];
+                wait_k(c);
+                if (c == 0) wait_q(0);
+                issue((uint32_t)((c + 2) % 3), 0, c, it.Lk16);
+            }
+            for (int q = 0; q < nqb; q++) {
+                for (int c = 0; c < nc; c++) {
+                    BK_TR(tw, 20);
+                    const uint32_t sb = nbj & 1;
+                    nbj++;
+                    issue(sb, q & 1, c, it.Lk16);
+                    if (q + 1 < nqb) {
+                        if (c == 0) wait_q((q + 1) & 1);  // first use of Q(q + 1)
+                        issue(2u, (q + 1) & 1, c, it.Lk16);
+                        if (c == nc - 1 && q + 2 < nqb) {
+                            // B(q, nc - 1) was the last reader of Q(q): refill its buffer with Q(q + 2), a whole round of pass-B jobs
+                            // before the first use
+                            wait_scores(sb);
+                            uint8_t *qd = sQ + (q & 1) * kAttQ * ROWB;
+                            uint64_t *bar = &bar_q[q & 1];
                             mbar_expect_tx_e(bar, (uint32_t)(kAttQ * ROWB));
-                            tma_load_2d_e(q, &tmQKV, bar, cq, it.t0 + (jq + 2) * kAttQ);
-                            tma_load_2d_e(q + 64 * ROWB, &tmQKV, bar, cq, it.t0 + (jq + 2) * kAttQ + 64);
+                            tma_load_2d_e(qd, &tmQKV, bar, cq, it.t0 + (q + 2) * kAttQ);
+                            tma_load_2d_e(qd + 64 * ROWB, &tmQKV, bar, cq, it.t0 + (q + 2) * kAttQ + 64);
                         }
-                        jc = 0; jq++;
+                    } else if (more) {
+                        // last query block: B(last, c) was the last reader of key chunk c -- refill it with the next item's keys as soon
+                        // as its MMAs have retired; with the first refill also the next Q(0), if its buffer is not the one this block reads
+                        wait_scores(sb);
+                        load_k(nxt, c);
+                        if (c == 0 && ((nqb - 1) & 1)) load_q01(nxt, 0);
+                        if (c >= 1 && c - 1 < pre_out) {  // pass A of the next item's first block, one chunk behind
+                            wait_k(c - 1);
+                            if (c == 1) wait_q(0);
+                            issue(2u, 0, c - 1, nxt.Lk16);
+                        }
                     }
                 }
             }
-            // the next item's Q(0), Q(1) and K: as soon as the last score MMAs of this item (and with them all earlier ones) have
-            // retired, i.e. under the last chunk's exponentials, its P.V MMAs and the output of the last block
-            if (item + istep < n_items) {
-                mbar_wait(&sfull[last_slot], ((par >> last_slot) & 1) ^ 1);
-                load_qk(pt_item(nx_t0, nx_L, (item + istep) % n_head));
+            if (more) {  // (every score MMA of this item has retired: see the last refill)
+                for (int c = nc; c < 4; c++) load_k(nxt, c);  // chunks the next item has beyond this one's
+                if (!((nqb - 1) & 1)) load_q01(nxt, 0);
+                load_q01(nxt, 1);
             }
+            pre_in = pre_out;
         }
     } else if (warp == CW + 1) {
         // ================================================================ P.V warp: [O | row sums] += P . [V | 1], P read from the score slot
@@ -283,13 +305,14 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         uint32_t pv_b = 0;  // pass-B jobs consumed
         uint32_t gb = 0;    // query blocks done by this CTA
         uint32_t vpar = 0;
+        int pre_in = 0;     // chunks of this item's A(0,*) done during the previous item (they went through slot 2)
         for (int item = item0; item < n_items; item += istep) {
             const PtItem it = pt_item(nx_t0, nx_L, item % n_head);
             fetch(item + istep, nx_t0, nx_L);
             BK_TR(tw, 19);
             // the prologue's chunks 1 and 2 went through the pass-B slots: the 16 warps report "read" on the P barriers, and the slot is
             // handed back the way it always is -- by a commit from this warp (nothing outstanding on it: it arrives at once)
-            for (int c = 1; c < it.nc && c < 3; c++) {
+            for (int c = pre_in > 1 ? pre_in : 1; c < it.nc && c < 3; c++) {
                 const uint32_t slot = (uint32_t)((c + 2) % 3);
                 mbar_wait(&pfull[slot * 2], (ppar >> slot) & 1);
                 mbar_wait(&pfull[slot * 2 + 1], (ppar >> slot) & 1);
@@ -325,10 +348,13 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
             }
             // the next item's V: when this item's last P.V MMAs have retired (the first P of the next item is a prologue and a chunk
             // of exponentials away)
-            if (item + istep < n_items) {
+            const bool more = item + istep < n_items;
+            const PtItem nxt = pt_item(nx_t0, nx_L, (item + istep) % n_head);
+            if (more) {
                 mbar_wait(bar_o, (gb - 1) & 1);
-                load_v(pt_item(nx_t0, nx_L, (item + istep) % n_head));
+                load_v(nxt);
             }
+            pre_in = pt_ahead(it, nxt, more);
         }
     } else if (warp >= CW + 2) {
         // ======================================================================= output warps: O * (1 / sum p) -> out rows
@@ -390,14 +416,22 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         uint32_t spar = 0;                                    // per score slot (bit): number of chunks consumed from it so far is odd
         uint32_t nb = 0;                                      // pass-B jobs done
         uint32_t gb = 0;                                      // query blocks done by this CTA
+        int pre_in = 0;                                       // chunks of this item's A(0,*) done during the previous item
+        float mx_next = -INFINITY;                            // running maximum of the block whose pass A is under way
+        int n2_t0, n2_L;  // the next item's length is needed during the current one: fetched two items ahead
+        fetch(item0 + istep, n2_t0, n2_L);
         for (int item = item0; item < n_items; item += istep) {
             const PtItem it = pt_item(nx_t0, nx_L, item % n_head);
-            fetch(item + istep, nx_t0, nx_L);
+            nx_t0 = n2_t0; nx_L = n2_L;
+            fetch(item + 2 * istep, n2_t0, n2_L);
             BK_TR(tw, 19);
-            const int L = it.L, nc = it.nc, nqb = it.nqb;
+            const int nc = it.nc, nqb = it.nqb;
+            const bool more = item + istep < n_items;
+            const PtItem nxt = pt_item(nx_t0, nx_L, (item + istep) % n_head);  // (valid if `more`)
+            const int pre_out = pt_ahead(it, nxt, more);
 
-            // one pass-A job: fold this group's 32 keys of chunk c into the running row maximum
-            auto step_a = [&](int c, float mx, uint32_t slot) {
+            // one pass-A job: fold this group's 32 keys of chunk c (of a sentence of L tokens) into the running row maximum
+            auto step_a = [&](int c, float mx, uint32_t slot, int L) {
                 BK_TR(tw, 7);
                 mbar_wait(&sfull[slot], (spar >> slot) & 1);
                 spar ^= 1u << slot;
@@ -428,8 +462,8 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                 return mx;
             };
 
-            float mx_next = -INFINITY;
-            for (int c = 0; c < nc; c++) mx_next = step_a(c, mx_next, (uint32_t)((c + 2) % 3));  // pass A of block 0 (not overlapped)
+            const int L = it.L;
+            for (int c = pre_in; c < nc; c++) mx_next = step_a(c, mx_next, (uint32_t)((c + 2) % 3), L);  // rest of pass A of block 0
             for (int qb = 0; qb < nqb; qb++, gb++) {
                 // ---- row maximum of this block over the four groups
                 float mx = mx_next;
@@ -489,10 +523,12 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                     if (lane == 0) mbar_arrive(&pfull[slot * 2 + psub]);
                     BK_TR(tw, 6);
                     nb++;
-                    // ---- pass A job of the next block, same chunk
-                    if (qb + 1 < nqb) mx_next = step_a(c, mx_next, 2u);
+                    // ---- pass A job of the next block, same chunk; in the last block: of the next item's first block, one chunk behind
+                    if (qb + 1 < nqb) mx_next = step_a(c, mx_next, 2u, L);
+                    else if (c >= 1 && c - 1 < pre_out) mx_next = step_a(c - 1, mx_next, 2u, nxt.L);
                 }
             }
+            pre_in = pre_out;
         }
     }
     BK_TR(tw, 14);
