@@ -95,9 +95,9 @@ __device__ __forceinline__ PtItem pt_item(int t0, int L, int head) {
 }
 
 // Chunks of the NEXT item's first maximum pass A(0,*) that run during this item's last query block (whose A slot is idle): chunk c - 1
-// behind B(last, c), once key chunk c - 1 holds the next item's keys.  Needs the next Q(0) in buffer 0 while the last block reads buffer 1.
+// behind B(last, c), once key chunk c - 1 holds the next item's keys.
 __device__ __forceinline__ int pt_ahead(const PtItem &it, const PtItem &nxt, bool more) {
-    if (!more || !((it.nqb - 1) & 1) || it.nc < 2) return 0;
+    if (!more || it.nc < 2) return 0;
     return it.nc - 1 < nxt.nc ? it.nc - 1 : nxt.nc;
 }
 
@@ -150,13 +150,13 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
     fetch(item0, nx_t0, nx_L);
 
     // Q(0), Q(1) and K of an item (score warp), V of an item (score warp for the first item, afterwards the P.V warp)
-    auto load_q01 = [&](const PtItem &it, int b) {  // query block b (0 or 1) -> Q buffer b
-        if (b >= it.nqb) return;
+    auto load_q = [&](const PtItem &it, int blk, int buf) {  // query block blk -> Q buffer buf
+        if (blk >= it.nqb) return;
         const int cq = it.head * DH;
-        uint8_t *q = sQ + b * kAttQ * ROWB;
-        mbar_expect_tx_e(&bar_q[b], (uint32_t)(kAttQ * ROWB));
-        tma_load_2d_e(q, &tmQKV, &bar_q[b], cq, it.t0 + b * kAttQ);
-        tma_load_2d_e(q + 64 * ROWB, &tmQKV, &bar_q[b], cq, it.t0 + b * kAttQ + 64);
+        uint8_t *q = sQ + buf * kAttQ * ROWB;
+        mbar_expect_tx_e(&bar_q[buf], (uint32_t)(kAttQ * ROWB));
+        tma_load_2d_e(q, &tmQKV, &bar_q[buf], cq, it.t0 + blk * kAttQ);
+        tma_load_2d_e(q + 64 * ROWB, &tmQKV, &bar_q[buf], cq, it.t0 + blk * kAttQ + 64);
     };
     auto load_k = [&](const PtItem &it, int c) {  // keys [128 c, 128 c + 128): two 64-row boxes, the last chunk possibly one
         if (c >= it.nc) return;
@@ -186,9 +186,9 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         __syncwarp();
         // the first item's loads (they need the barriers only): their latency runs under the TMEM allocation and the CTA-wide sync
         const PtItem it = pt_item(nx_t0, nx_L, item0 % n_head);
-        load_q01(it, 0);
+        load_q(it, 0, 0);
         for (int c = 0; c < 4; c++) load_k(it, c);
-        load_q01(it, 1);
+        load_q(it, 1, 1);
         load_v(it);
     } else if (warp == CW + 1) {  // meanwhile: the all-ones tile and the TMEM allocation
         for (int i = lane; i < 16 * ROWB / 4; i += 32) reinterpret_cast<uint32_t *>(sOnes)[i] = 0x3C003C00u;
@@ -213,6 +213,7 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
         uint32_t kpar = 0, qpar = 0;      // per K-chunk / Q-buffer barrier (bit): parity of the next phase to wait for
         uint32_t nbj = 0;                 // pass-B jobs issued
         int pre_in = 0;                   // chunks of this item's A(0,*) done during the previous item
+        int qoff = 0;                     // block q of the item reads Q buffer (q + qoff) % 2: Q(0) goes where the previous item's last block is not
         const uint64_t dk0 = umma_desc_kmajor<ROWB>(smem_u32(sK));
         const uint64_t dq0 = umma_desc_kmajor<ROWB>(smem_u32(sQ));
         auto wait_k = [&](int c) { mbar_wait(&bar_k[c], (kpar >> c) & 1); kpar ^= 1u << c; };
@@ -249,52 +250,49 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
             const PtItem nxt = pt_item(nx_t0, nx_L, (item + istep) % n_head);  // (valid if `more`)
             const int pre_out = pt_ahead(it, nxt, more);
             const int nqb = it.nqb, nc = it.nc;
-            const int cq = it.head * DH;
+            const int lastbuf = (nqb - 1 + qoff) & 1;  // the buffer the last query block reads
             for (int c = pre_in; c < nc; c++) {  // prologue: pass A of block 0
                 BK_TR(tw, 20);
                 wait_k(c);
-                if (c == 0) wait_q(0);
-                issue((uint32_t)((c + 2) % 3), 0, c, it.Lk16);
+                if (c == 0) wait_q(qoff);
+                issue((uint32_t)((c + 2) % 3), qoff, c, it.Lk16);
             }
             for (int q = 0; q < nqb; q++) {
+                const int qbuf = (q + qoff) & 1;
                 for (int c = 0; c < nc; c++) {
                     BK_TR(tw, 20);
                     const uint32_t sb = nbj & 1;
                     nbj++;
-                    issue(sb, q & 1, c, it.Lk16);
+                    issue(sb, qbuf, c, it.Lk16);
                     if (q + 1 < nqb) {
-                        if (c == 0) wait_q((q + 1) & 1);  // first use of Q(q + 1)
-                        issue(2u, (q + 1) & 1, c, it.Lk16);
+                        if (c == 0) wait_q(qbuf ^ 1);  // first use of Q(q + 1)
+                        issue(2u, qbuf ^ 1, c, it.Lk16);
                         if (c == nc - 1 && q + 2 < nqb) {
                             // B(q, nc - 1) was the last reader of Q(q): refill its buffer with Q(q + 2), a whole round of pass-B jobs
                             // before the first use
                             wait_scores(sb);
-                            uint8_t *qd = sQ + (q & 1) * kAttQ * ROWB;
-                            uint64_t *bar = &bar_q[q & 1];
-                            mbar_expect_tx_e(bar, (uint32_t)(kAttQ * ROWB));
-                            tma_load_2d_e(qd, &tmQKV, bar, cq, it.t0 + (q + 2) * kAttQ);
-                            tma_load_2d_e(qd + 64 * ROWB, &tmQKV, bar, cq, it.t0 + (q + 2) * kAttQ + 64);
+                            load_q(it, q + 2, qbuf);
                         }
                     } else if (more) {
                         // last query block: B(last, c) was the last reader of key chunk c -- refill it with the next item's keys as soon
-                        // as its MMAs have retired; with the first refill also the next Q(0), if its buffer is not the one this block reads
+                        // as its MMAs have retired; with the first refill also the next Q(0), into the buffer this block does not read
                         wait_scores(sb);
                         load_k(nxt, c);
-                        if (c == 0 && ((nqb - 1) & 1)) load_q01(nxt, 0);
+                        if (c == 0) load_q(nxt, 0, lastbuf ^ 1);
                         if (c >= 1 && c - 1 < pre_out) {  // pass A of the next item's first block, one chunk behind
                             wait_k(c - 1);
-                            if (c == 1) wait_q(0);
-                            issue(2u, 0, c - 1, nxt.Lk16);
+                            if (c == 1) wait_q(lastbuf ^ 1);
+                            issue(2u, lastbuf ^ 1, c - 1, nxt.Lk16);
                         }
                     }
                 }
             }
             if (more) {  // (every score MMA of this item has retired: see the last refill)
                 for (int c = nc; c < 4; c++) load_k(nxt, c);  // chunks the next item has beyond this one's
-                if (!((nqb - 1) & 1)) load_q01(nxt, 0);
-                load_q01(nxt, 1);
+                load_q(nxt, 1, lastbuf);
             }
             pre_in = pre_out;
+            qoff = lastbuf ^ 1;
         }
     } else if (warp == CW + 1) {
         // ================================================================ P.V warp: [O | row sums] += P . [V | 1], P read from the score slot
