@@ -74,6 +74,10 @@ __device__ unsigned long long g_att_trace[8][1024];
 #define BK_TR(w, tag)
 #endif
 
+#ifndef BK_PT_STAGGER
+#define BK_PT_STAGGER 1
+#endif
+constexpr bool kPtStagger = BK_PT_STAGGER != 0;
 constexpr int kPtThreads = kStreamThreads + 128;  // 16 softmax warps, score warp, P.V warp, 4 output warps
 constexpr int kPtTail = 192 + 2 * 2048 + 4 * 2048;  // barriers + TMEM slot, two row-maximum exchange buffers, output staging
 
@@ -476,7 +480,17 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                 }
                 mx *= scale;  // max(s*scale) == max(s)*scale for scale > 0 (rounding is monotonic)
                 mx_next = -INFINITY;
+                // ---- the A slot's job of this step: pass A of the next block, same chunk; in the last block: of the next item's first
+                // block, one chunk behind.  The warps of the first 64-key half take it after their pass-B job, those of the second half
+                // BEFORE it: the two halves -- two warps each on every scheduler -- then run about half a step apart, one half's
+                // exponentials (the MUFU is what bounds this kernel) under the other half's loads, stores, barriers and maximum pass,
+                // instead of four warps queueing for the MUFU and then leaving it idle together.
+                auto pass_a = [&](int c) {
+                    if (qb + 1 < nqb) mx_next = step_a(c, mx_next, 2u, L);
+                    else if (c >= 1 && c - 1 < pre_out) mx_next = step_a(c - 1, mx_next, 2u, nxt.L);
+                };
                 for (int c = 0; c < nc; c++) {
+                    if (kPtStagger && psub == 1) pass_a(c);
                     // ---- pass B job: p = f16(exp(f16(s*scale - max))) for my 32 keys of chunk c, written back over the scores
                     const uint32_t slot = nb & 1;
                     BK_TR(tw, 1);
@@ -521,9 +535,7 @@ attention_pt_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *__
                     if (lane == 0) mbar_arrive(&pfull[slot * 2 + psub]);
                     BK_TR(tw, 6);
                     nb++;
-                    // ---- pass A job of the next block, same chunk; in the last block: of the next item's first block, one chunk behind
-                    if (qb + 1 < nqb) mx_next = step_a(c, mx_next, 2u, L);
-                    else if (c >= 1 && c - 1 < pre_out) mx_next = step_a(c - 1, mx_next, 2u, nxt.L);
+                    if (!kPtStagger || psub == 0) pass_a(c);
                 }
             }
             pre_in = pre_out;
