@@ -14,6 +14,35 @@
 #pragma once
 
 constexpr int kLoopThreads = 160;  // 4 softmax warps + control warp
+constexpr int kLoopStage = 4 * 1024; // output staging, 1 KB per softmax warp
+
+// A warp's 32 rows x 64 bytes (32 f16 features of 32 query rows, one row per lane, pk = 16 f16 pairs) -> global memory through a 1 KB
+// staging tile, 16 rows at a time, so that one store instruction covers 8 rows x 64 contiguous bytes (full 32-byte sectors) instead
+// of 32 rows x 16 bytes.  Stores of the direct form -- every lane its own row, 16 bytes per instruction -- are 32 half-sector
+// transactions each and back up the SM's load/store path, which the mbarrier operations of every resident CTA share (measured on the
+// kernel for longer sentences, attention_pt.cuh: 13 %).  `my_dst`: where this lane's row goes (its 64 bytes), nullptr for a row past
+// the sentence.  Chunk c of staged row R sits at 16-byte position (c + R / 2) % 4 of the row: conflict-free both ways.
+__device__ __forceinline__ void store_rows64_1k(uint8_t *stage, const uint32_t (&pk)[16], __half *my_dst, int lane) {
+    const unsigned long long mine = reinterpret_cast<unsigned long long>(my_dst);
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+        if ((lane >> 4) == hh) {
+            const int rr = lane & 15;
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                *reinterpret_cast<uint4 *>(stage + rr * 64 + (((q + (rr >> 1)) & 3) << 4)) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            const int R = 8 * j + (lane >> 2), c = lane & 3;
+            const uint4 v = *reinterpret_cast<const uint4 *>(stage + R * 64 + (((c + (R >> 1)) & 3) << 4));
+            const unsigned long long dst = __shfl_sync(0xffffffffu, mine, hh * 16 + R);
+            if (dst) *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(dst) + c * 8) = v;
+        }
+        __syncwarp();
+    }
+}
 
 template <int DH>
 __global__ void __launch_bounds__(kLoopThreads, 4)
@@ -32,6 +61,7 @@ attention_loop_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *
     uint64_t *bar_v = bar_qk + 1, *bar_s = bar_qk + 2, *bar_o = bar_qk + 3, *bar_tfree = bar_qk + 4, *pfull = bar_qk + 5;  // pfull[2]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_qk + 7);
     uint32_t *ones = reinterpret_cast<uint32_t *>(bar_qk + 8);  // 512 B
+    uint8_t *stage = tail + 64 + 512;                           // [4 warps][1 KB] output staging
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     pdl_launch_dependents();
@@ -219,13 +249,10 @@ attention_loop_kernel(const __grid_constant__ CUtensorMap tmQKV, const int32_t *
 #pragma unroll
                     for (int i = 0; i < 32; i++) o[i] = q8_round(o[i], id, dq8);
                 }
-                if (r < L) {
-                    uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)(t0 + r) * d + (size_t)head * DH + hc * 32);
+                uint32_t pk[16];
 #pragma unroll
-                    for (int q = 0; q < 4; q++)
-                        dst[q] = make_uint4(pack_h2(o[8 * q], o[8 * q + 1]), pack_h2(o[8 * q + 2], o[8 * q + 3]),
-                                            pack_h2(o[8 * q + 4], o[8 * q + 5]), pack_h2(o[8 * q + 6], o[8 * q + 7]));
-                }
+                for (int i = 0; i < 16; i++) pk[i] = pack_h2(o[2 * i], o[2 * i + 1]);
+                store_rows64_1k(stage + quad * 1024, pk, r < L ? out + (size_t)(t0 + r) * d + (size_t)head * DH + hc * 32 : nullptr, lane);
             }
         }
     }
@@ -242,7 +269,7 @@ static cudaError_t launch_att_loop(const CUtensorMap &tm, const int32_t *cu, int
                                    cudaStream_t st) {
     constexpr int ROWB = DH * 2;
     constexpr int R0 = 2 * kAttQ * ROWB > 2 * kAttQ * 128 ? 2 * kAttQ * ROWB : 2 * kAttQ * 128;
-    constexpr size_t smem = R0 + kAttQ * ROWB + 64 + 512;
+    constexpr size_t smem = R0 + kAttQ * ROWB + 64 + 512 + kLoopStage;
     static int sms[64] = {0};
     int dev = 0;
     cudaGetDevice(&dev);

@@ -43,6 +43,7 @@ attention_pack_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_con
     uint64_t *bar_v = bar_qk + 1, *bar_s = bar_qk + 2, *bar_o = bar_qk + 3, *bar_tfree = bar_qk + 4, *pfull = bar_qk + 5;  // pfull[2]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_qk + 7);
     uint32_t *ones = reinterpret_cast<uint32_t *>(bar_qk + 8);  // 512 B
+    uint8_t *stage = tail + 64 + 512;                           // [4 warps][1 KB] output staging (store_rows64_1k, attention_loop.cuh)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_items = pack_tiles(pc) * n_head;
@@ -228,13 +229,10 @@ attention_pack_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_con
 #pragma unroll
                     for (int i = 0; i < 32; i++) o[i] = q8_round(o[i], id, dq8);
                 }
-                if (qi < L) {
-                    uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)(t0 + qi) * d + (size_t)head * DH + hc * 32);
+                uint32_t pk[16];
 #pragma unroll
-                    for (int q = 0; q < 4; q++)
-                        dst[q] = make_uint4(pack_h2(o[8 * q], o[8 * q + 1]), pack_h2(o[8 * q + 2], o[8 * q + 3]),
-                                            pack_h2(o[8 * q + 4], o[8 * q + 5]), pack_h2(o[8 * q + 6], o[8 * q + 7]));
-                }
+                for (int i = 0; i < 16; i++) pk[i] = pack_h2(o[2 * i], o[2 * i + 1]);
+                store_rows64_1k(stage + quad * 1024, pk, qi < L ? out + (size_t)(t0 + qi) * d + (size_t)head * DH + hc * 32 : nullptr, lane);
             }
         }
     }
@@ -252,7 +250,7 @@ static cudaError_t launch_att_pack(const CUtensorMap &tm64, const CUtensorMap &t
                                    const PackCounts &pc, int d, int n_head, __half *out, int qmode, cudaStream_t st) {
     constexpr int ROWB = DH * 2;
     constexpr int R0 = 2 * kAttQ * ROWB > 2 * kAttQ * 128 ? 2 * kAttQ * ROWB : 2 * kAttQ * 128;
-    constexpr size_t smem = R0 + kAttQ * ROWB + 64 + 512;
+    constexpr size_t smem = R0 + kAttQ * ROWB + 64 + 512 + kLoopStage;
     static int sms[64] = {0};
     int dev = 0;
     cudaGetDevice(&dev);
