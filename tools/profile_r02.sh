@@ -19,5 +19,5 @@ ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start o
 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'attention|gemm_ln|embed_ln|pool_norm|batch_' -c 8 -o $OUT/${TAG}_full_f16 -f $CMD_F16 > $OUT/${TAG}_ncu_full_f16.log 2>&1
 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'gemm_tcgen05' -c 2 -o $OUT/${TAG}_full_f16_gemm -f $CMD_F16 > $OUT/${TAG}_ncu_full_f16_gemm.log 2>&1
 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'gemm_ln|embed_ln|gemm_tcgen05' -c 5 -o $OUT/${TAG}_full_q4_0 -f $CMD_Q4 > $OUT/${TAG}_ncu_full_q4.log 2>&1
-ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'attention_stream' -c 1 -o $OUT/${TAG}_full_varlen -f $CMD_VAR > $OUT/${TAG}_ncu_full_varlen.log 2>&1
+ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'attention_pt|attention_stream' -c 1 -o $OUT/${TAG}_full_varlen -f $CMD_VAR > $OUT/${TAG}_ncu_full_varlen.log 2>&1
 ls -la $OUT/${TAG}_*
