@@ -19,7 +19,7 @@ $(BUILD)/libbert.so: $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -cudart static -lpthread -ldl -lrt
 	ln -sf libbert.so $(BUILD)/libbert_shared.so
 
-$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/gemm_parts.cuh $(SRC)/attention_persist.cuh $(SRC)/attention_loop.cuh $(SRC)/attention_pack.cuh $(SRC)/attention_stream.cuh $(SRC)/attention_duo.cuh $(SRC)/attention_pt.cuh $(SRC)/kernels.h include/bk_api.h | $(OBJ)
+$(OBJ)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/gemm_parts.cuh $(SRC)/attention_persist.cuh $(SRC)/attention_loop.cuh $(SRC)/attention_pack.cuh $(SRC)/attention_stream.cuh $(SRC)/attention_duo.cuh $(SRC)/attention_pt.cuh $(SRC)/attention_xs.cuh $(SRC)/kernels.h include/bk_api.h | $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(OBJ)/$*.ptxas.log || (cat $(OBJ)/$*.ptxas.log; false)
 
 $(OBJ)/%.o: $(SRC)/%.cpp $(SRC)/gguf.h $(SRC)/tokenizer_wp.h include/bert.h include/bk_api.h | $(OBJ)

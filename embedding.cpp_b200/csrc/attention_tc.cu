@@ -31,6 +31,7 @@
 namespace bk {
 
 constexpr int kAttQ = 128;  // queries per CTA
+constexpr bool kAttXsDefault = false;    // attention_xs.cuh for launches with sentences > 128 tokens (A/B: BERT_B200_ATT_XS)
 constexpr bool kAttPtDefault = true;     // attention_pt.cuh for launches with sentences > 128 tokens (A/B: BERT_B200_ATT_PT)
 constexpr bool kAttDuoDefault = false;   // attention_duo.cuh for launches with sentences > 128 tokens (A/B: BERT_B200_ATT_DUO)
 constexpr bool kAttLoopDefault = true;   // attention_loop.cuh for launches of sentences <= 128 tokens (A/B: BERT_B200_ATT_LOOP)
@@ -399,6 +400,7 @@ __global__ void __launch_bounds__(32 + 128 * G) attention_tc_kernel(const __grid
 #include "attention_stream.cuh"
 #include "attention_duo.cuh"
 #include "attention_pt.cuh"
+#include "attention_xs.cuh"
 
 template <int DH, int G>
 static cudaError_t launch_att(const CUtensorMap &tm, const int32_t *cu, int n_seq, int max_len, int d, int n_head, __half *out,
@@ -451,6 +453,12 @@ cudaError_t launch_attention(const CUtensorMap &tmQKV, const int32_t *cu_seqlens
     // launches with sentences of more than 128 tokens: scores streamed through a TMEM ring (BERT_B200_ATT_STREAM=0: whole
     // score block resident, attention_tc_kernel)
     const char *sv = getenv("BERT_B200_ATT_STREAM");
+    // exp / service warp split (attention_xs.cuh); BERT_B200_ATT_XS=0: attention_pt.cuh
+    const char *xv = getenv("BERT_B200_ATT_XS");
+    if (max_len > kAttQ && (!sv || atoi(sv) != 0) && env_g == 0 && (xv ? atoi(xv) != 0 : kAttXsDefault)) {
+        if (dh == 64) return launch_att_xs<64>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
+        if (dh == 32) return launch_att_xs<32>(tmQKV, cu_seqlens, n_seq, max_len, d, n_head, out, qmode, st);
+    }
     // P kept in tensor memory (attention_pt.cuh); BERT_B200_ATT_PT=0: through shared memory (attention_stream.cuh)
     const char *tv = getenv("BERT_B200_ATT_PT");
     if (max_len > kAttQ && (!sv || atoi(sv) != 0) && env_g == 0 && (tv ? atoi(tv) != 0 : kAttPtDefault)) {

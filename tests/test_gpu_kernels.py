@@ -313,16 +313,18 @@ def test_attention_streaming_kernel(lib, orc, make_model, monkeypatch, d, H, qmo
     qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
     L = np.array(lens, np.int32)
     outs = []
-    # P in tensor memory (attention_pt.cuh) / two blocks in flight (attention_duo.cuh) / streaming through shared memory / resident scores
-    for stream, pt, duo in (("1", "1", "0"), ("1", "0", "1"), ("1", "0", "0"), ("0", "0", "0")):
+    # exp / service warps (attention_xs.cuh) / P in tensor memory (attention_pt.cuh) / two blocks in flight (attention_duo.cuh) /
+    # streaming through shared memory / resident scores
+    for stream, xs, pt, duo in (("1", "1", "0", "0"), ("1", "0", "1", "0"), ("1", "0", "0", "1"), ("1", "0", "0", "0"), ("0", "0", "0", "0")):
         monkeypatch.setenv("BERT_B200_ATT_STREAM", stream)
+        monkeypatch.setenv("BERT_B200_ATT_XS", xs)
         monkeypatch.setenv("BERT_B200_ATT_PT", pt)
         monkeypatch.setenv("BERT_B200_ATT_DUO", duo)
         out = np.zeros((T, d), np.float16)
         assert lib.bk_test_attention(0, len(lens), L.ctypes.data_as(_i32p), d, H, u16(qkv), qmode, u16(out)) == 0
         outs.append(out)
-    for k in range(3):
-        assert np.array_equal(outs[k].view(np.uint16), outs[3].view(np.uint16)), k
+    for k in range(4):
+        assert np.array_equal(outs[k].view(np.uint16), outs[4].view(np.uint16)), k
     if qmode == 0:
         o = orc.Oracle(make_model("tiny", "f32", 13, 300))
         off = 0

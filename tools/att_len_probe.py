@@ -27,5 +27,5 @@ for L in LENS:
     eng.run_staged(4, time_kernels=True)
     ms, n = eng.kernel_ms()["attention"]
     row.append(f"L={L}: {1e3 * ms / n:.1f} us")
-print(f"{ftype} LOOP={os.environ.get('BERT_B200_ATT_LOOP', 'default')} PERSIST={os.environ.get('BERT_B200_ATT_PERSIST', 'default')} STREAM={os.environ.get('BERT_B200_ATT_STREAM', 'default')} PACK={os.environ.get('BERT_B200_ATT_PACK', 'default')} DUO={os.environ.get('BERT_B200_ATT_DUO', 'default')} PT={os.environ.get('BERT_B200_ATT_PT', 'default')}: " + "  ".join(row), flush=True)
+print(f"{ftype} LOOP={os.environ.get('BERT_B200_ATT_LOOP', 'default')} PERSIST={os.environ.get('BERT_B200_ATT_PERSIST', 'default')} STREAM={os.environ.get('BERT_B200_ATT_STREAM', 'default')} PACK={os.environ.get('BERT_B200_ATT_PACK', 'default')} DUO={os.environ.get('BERT_B200_ATT_DUO', 'default')} PT={os.environ.get('BERT_B200_ATT_PT', 'default')} XS={os.environ.get('BERT_B200_ATT_XS', 'default')}: " + "  ".join(row), flush=True)
 eng.close()

@@ -30,7 +30,7 @@ NAMES = {0: "entry", 13: "after-setup-sync", 14: "done", 15: "after-exit-sync", 
          6: "B:handed", 7: "A:wait-S", 8: "A:S-ready", 9: "A:done", 10: "max:publish", 11: "max:synced", 12: "epilogue-done", 19: "ITEM",
          16: "epi:O-complete", 17: "epi:O-loaded", 18: "epi:scaled", 20: "S:job", 21: "S:waits-done", 22: "S:committed", 30: "PV:wait0", 31: "PV:wait1", 32: "PV:P0-ready", 33: "PV:P1-ready", 34: "PV:committed"}
 t0 = min(int(tr[w][0] & 0xFFFFFFFFFFFF) for w in range(7) if tr[w][0])
-for w, name in enumerate(["softmax warp 0 (g0)", "softmax warp 5 (g1)", "softmax warp 10 (g2)", "softmax warp 15 (g3)", "score warp", "P.V warp", "output warp 20"]):
+for w, name in enumerate(os.environ.get("TRACE_NAMES", "softmax warp 0 (g0),softmax warp 5 (g1),softmax warp 10 (g2),softmax warp 15 (g3),score warp,P.V warp,output warp 20").split(",")):
     print(f"== {name}")
     prev = None
     for v in tr[w]:
