@@ -302,13 +302,16 @@ def test_attention_persistent_kernel(lib, orc, make_model, monkeypatch, d, H, n_
             off += n
 
 
-@pytest.mark.parametrize("d,H,qmode", [(768, 12, 0), (384, 12, 0), (256, 4, 1), (128, 4, 2)])
-def test_attention_streaming_kernel(lib, orc, make_model, monkeypatch, d, H, qmode):
+@pytest.mark.parametrize("d,H,qmode,reps", [(768, 12, 0, 1), (384, 12, 0, 1), (256, 4, 1, 1), (128, 4, 2, 1),
+                                             (256, 4, 1, 5), (128, 4, 2, 7)])   # reps > 1: several items per persistent CTA with the Q8 epilogue
+def test_attention_streaming_kernel(lib, orc, make_model, monkeypatch, d, H, qmode, reps):
     """launches with sentences of more than 128 tokens stream the scores through a two-slot TMEM ring and compute them
     twice (attention_stream.cuh): every chunk / query-block boundary, short sentences inside a long launch, against the
     oracle and bit for bit against the kernel that keeps the whole score block resident"""
     rng = np.random.default_rng(d + qmode)
     lens = [512, 511, 385, 384, 383, 300, 257, 256, 255, 200, 129, 128, 127, 100, 64, 33, 17, 16, 5, 1] + [int(v) for v in rng.integers(1, 513, 12)]
+    for _ in range(reps - 1):
+        lens += [int(v) for v in rng.integers(1, 513, 32)]
     T = sum(lens)
     qkv = h(rng.standard_normal((T, 3 * d)) * 1.2)
     L = np.array(lens, np.int32)
